@@ -1,0 +1,754 @@
+// X4-X9 of the hot path: one boosting round of depth-wise histogram tree growth for a whole wave of
+// (individual x fold) jobs at once, plus the per-round CV metric and early-stopping bookkeeping.
+//
+// Replaces the inner loop of xgb.cv as gentun calls it
+// (/root/reference/gentun/models/xgboost_models.py:33-36): for every round, for every fold,
+// Booster.update (objective gradient -> per-level histogram -> split enumeration -> row partition ->
+// leaf values -> prediction cache) and Booster.eval_set + aggcv + EarlyStopping.
+// Arithmetic follows upstream xgboost >= 2.0 tree_method=hist: src/tree/param.h (CalcWeight,
+// CalcGainGivenWeight, ThresholdL1), src/tree/split_evaluator.h, src/tree/hist/evaluate_splits.h
+// (EnumerateSplit<+1>, CPUExpandEntry::IsValid), src/objective/regression_obj.cu,
+// src/metric/elementwise_metric.cu, python-package/xgboost/callback.py (EarlyStopping).
+//
+// Numeric design: gradients are quantised once per round to fixed point (power-of-two scale,
+// |q| <= 2^19) so that all histogram arithmetic is integer: shared-memory partials are int32
+// (native ATOMS.ADD), global cells are int64, parent - child subtraction is exact and the result
+// does not depend on summation order.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace gt {
+namespace {
+
+constexpr float kRtEps = 1e-6f;
+constexpr int kHistThreads = 256;
+constexpr int kHistSmem = 2 * kBins * kLanes * (int)sizeof(int);   // g plane + h plane = 64 KiB
+
+// ------------------------------------------------------------------ split arithmetic
+__device__ __forceinline__ double thr_l1(double w, float alpha) {
+  if (w > +alpha) return w - alpha;
+  if (w < -alpha) return w + alpha;
+  return 0.0;
+}
+__device__ __forceinline__ float calc_weight(const JobParams& p, double G, double H) {
+  if (H < p.mcw || H <= 0.0) return 0.0f;
+  double dw = -thr_l1(G, p.alpha) / (H + p.lambda);
+  if (p.mds != 0.0f && fabs(dw) > p.mds) dw = copysign((double)p.mds, dw);
+  return (float)dw;
+}
+__device__ __forceinline__ float gain_given_weight(const JobParams& p, double G, double H, float w) {
+  if (H <= 0) return 0.0f;
+  if (p.mds == 0.0f) {
+    double t = thr_l1(G, p.alpha);
+    return (float)((t * t) / (H + p.lambda));
+  }
+  float g = (float)G, h = (float)H;
+  return -(2.0f * g * w + (h + p.lambda) * (w * w));
+}
+__device__ __forceinline__ float calc_gain(const JobParams& p, double G, double H) {
+  return gain_given_weight(p, G, H, calc_weight(p, G, H));
+}
+__device__ __forceinline__ float split_gain(const JobParams& p, double GL, double HL, double GR, double HR) {
+  float wl = calc_weight(p, GL, HL), wr = calc_weight(p, GR, HR);
+  return gain_given_weight(p, GL, HL, wl) + gain_given_weight(p, GR, HR, wr);
+}
+__device__ __forceinline__ float sigmoid_x(float x) {   // upstream common::Sigmoid
+  x = fminf(-x, 88.7f);
+  float denom = expf(x) + 1.0f + 1e-16f;
+  return 1.0f / denom;
+}
+__device__ __forceinline__ void grad_pair(int objective, float pred, float y, float spw, float& g, float& h) {
+  float wgt = (y == 1.0f) ? spw : 1.0f;
+  if (objective == 1) {
+    float p = sigmoid_x(pred);
+    g = (p - y) * wgt;
+    h = fmaxf(p * (1.0f - p), 1e-16f) * wgt;
+  } else {
+    g = (pred - y) * wgt;
+    h = 1.0f * wgt;
+  }
+}
+
+__device__ __forceinline__ int level_first(int level) { return (1 << level) - 1; }
+
+// ------------------------------------------------------------------ round set-up / tear-down
+__device__ void prepare_next_round(const Wave& w, int j) {
+  JobState& js = w.js[j];
+  const JobParams& jp = w.jp[j];
+  float gmax = __uint_as_float(js.gmax_bits), hmax = __uint_as_float(js.hmax_bits);
+  int e;
+  float sg = 1.0f, sh = 1.0f;
+  if (gmax > 0.f && isfinite(gmax)) { frexpf(gmax, &e); sg = ldexpf(1.0f, kQuantBits - e); }
+  if (hmax > 0.f && isfinite(hmax)) { frexpf(hmax, &e); sh = ldexpf(1.0f, kQuantBits - e); }
+  js.sg = sg; js.sh = sh;
+  js.inv_sg = 1.0 / (double)sg; js.inv_sh = 1.0 / (double)sh;
+  js.gmax_bits = 0u; js.hmax_bits = 0u;
+  Node& r = w.nodes[(size_t)j * kNodeCap];
+  r.G = 0; r.H = 0; r.begin = 0; r.cnt = (uint32_t)w.folds[jp.fold].ntrain;
+  r.leaf = 0.f; r.root_gain = 0.f; r.loss_chg = 0.f; r.feat = -1; r.bin = 0; r.state = kOpen; r.buf = 0;
+  TreeNode& t = w.tree[(size_t)j * kNodeCap];
+  t.leaf = 0.f; t.feat = -1; t.bin = 0; t.state = kOpen;
+}
+
+// pred = base margin; record max |g|, max h of round 0
+__global__ void __launch_bounds__(256) k_init_wave(Wave w) {
+  const int j = blockIdx.y;
+  const JobParams jp = w.jp[j];
+  const FoldDev fd = w.folds[jp.fold];
+  float* pred = w.pred + (size_t)j * w.n;
+  const long long r0 = (long long)blockIdx.x * kPredRows;
+  float gm = 0.f, hm = 0.f;
+  for (int i = threadIdx.x; i < kPredRows; i += blockDim.x) {
+    long long r = r0 + i;
+    if (r >= w.n) break;
+    pred[r] = jp.base_margin;
+    if (r < fd.ntrain) {
+      float g, h;
+      grad_pair(w.objective, jp.base_margin, fd.y[r], jp.spw, g, h);
+      gm = fmaxf(gm, fabsf(g)); hm = fmaxf(hm, fabsf(h));
+    }
+  }
+  for (int d = 16; d; d >>= 1) { gm = fmaxf(gm, __shfl_xor_sync(0xffffffffu, gm, d)); hm = fmaxf(hm, __shfl_xor_sync(0xffffffffu, hm, d)); }
+  if ((threadIdx.x & 31) == 0) {
+    if (gm > 0.f) atomicMax(&w.js[j].gmax_bits, __float_as_uint(gm));
+    if (hm > 0.f) atomicMax(&w.js[j].hmax_bits, __float_as_uint(hm));
+  }
+}
+
+// X4: objective gradient, row subsampling, fixed-point quantisation, root sums, identity row set
+__global__ void __launch_bounds__(256) k_grad(Wave w) {
+  const int j = blockIdx.y;
+  const JobState& js = w.js[j];
+  if (!js.active) return;
+  const JobParams jp = w.jp[j];
+  const FoldDev fd = w.folds[jp.fold];
+  const int round = w.is[jp.ind].round;
+  const float* pred = w.pred + (size_t)j * w.n;
+  int2* gq = w.gq + (size_t)j * w.nt_stride;
+  uint32_t* ridx = w.ridx + (size_t)j * 2 * w.nt_stride;
+  Node* nodes = w.nodes + (size_t)j * kNodeCap;
+  if (blockIdx.x == 0)
+    for (int i = 1 + threadIdx.x; i < kNodeCap; i += blockDim.x) nodes[i].state = kAbsent;
+  const uint64_t skey = stream_key(1u, (uint32_t)jp.fold, (uint32_t)round, 0u);
+  const bool sub = jp.subsample < 1.0f;
+  long long sG = 0, sH = 0;
+  const long long r0 = (long long)blockIdx.x * kPredRows;
+  for (int i = threadIdx.x; i < kPredRows; i += blockDim.x) {
+    long long r = r0 + i;
+    if (r >= fd.ntrain) break;
+    float g, h;
+    grad_pair(w.objective, pred[r], fd.y[r], jp.spw, g, h);
+    if (sub && !(u01(draw64(skey, (uint64_t)r)) < jp.subsample)) { g = 0.f; h = 0.f; }
+    int qg = __float2int_rn(g * js.sg), qh = __float2int_rn(h * js.sh);
+    gq[r] = make_int2(qg, qh);
+    ridx[r] = (uint32_t)r;
+    sG += qg; sH += qh;
+  }
+  for (int d = 16; d; d >>= 1) { sG += __shfl_xor_sync(0xffffffffu, sG, d); sH += __shfl_xor_sync(0xffffffffu, sH, d); }
+  __shared__ long long s_g[8], s_h[8];
+  const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) { s_g[wid] = sG; s_h[wid] = sH; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    long long a = 0, b = 0;
+    for (int q = 0; q < 8; ++q) { a += s_g[q]; b += s_h[q]; }
+    if (a) atomicAdd(reinterpret_cast<unsigned long long*>(&nodes[0].G), (unsigned long long)a);
+    if (b) atomicAdd(reinterpret_cast<unsigned long long*>(&nodes[0].H), (unsigned long long)b);
+  }
+}
+
+// ------------------------------------------------------------------ per-level planning
+// ColumnSampler stand-in: keep the n candidates with the smallest (draw, index).
+__device__ void sample_mask(uint64_t key, const uint32_t* in_mask, int f, int n_keep, uint32_t* out_mask /* smem */) {
+  for (int q = threadIdx.x; q < kMaskWords; q += blockDim.x) out_mask[q] = 0u;
+  __syncthreads();
+  for (int jf = threadIdx.x; jf < f; jf += blockDim.x) {
+    if (!((in_mask[jf >> 5] >> (jf & 31)) & 1u)) continue;
+    uint64_t kj = draw64(key, (uint64_t)jf);
+    int rank = 0;
+    for (int i = 0; i < f; ++i) {
+      if (!((in_mask[i >> 5] >> (i & 31)) & 1u)) continue;
+      uint64_t ki = draw64(key, (uint64_t)i);
+      rank += (ki < kj) || (ki == kj && i < jf);
+    }
+    if (rank < n_keep) atomicOr(&out_mask[jf >> 5], 1u << (jf & 31));
+  }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(256) k_plan_hist(Wave w, int level) {
+  const int j = blockIdx.x;
+  JobState& js = w.js[j];
+  const JobParams jp = w.jp[j];
+  __shared__ uint32_t s_mask[kMaskWords];
+  __shared__ uint32_t s_in[kMaskWords];
+  if (threadIdx.x == 0) { js.n_hist_items = 0; js.n_pairs = 0; js.n_zero = 0; js.n_part_items = 0; }
+  if (!js.active || level >= jp.max_depth) return;
+  const int round = w.is[jp.ind].round;
+  // feature sets (colsample_bytree at level 0, colsample_bylevel at every level)
+  if (level == 0) {
+    for (int q = threadIdx.x; q < kMaskWords; q += blockDim.x) {
+      uint32_t m = 0u;
+      for (int b = 0; b < 32; ++b) if (q * 32 + b < w.f) m |= 1u << b;
+      s_in[q] = m;
+    }
+    __syncthreads();
+    int n_tree = w.f;
+    if (jp.coltree != 1.0f) {
+      n_tree = (int)(jp.coltree * (float)w.f); if (n_tree < 1) n_tree = 1;
+      sample_mask(stream_key(2u, (uint32_t)jp.fold, (uint32_t)round, 0u), s_in, w.f, n_tree, s_mask);
+      for (int q = threadIdx.x; q < kMaskWords; q += blockDim.x) js.tmask[q] = s_mask[q];
+    } else {
+      for (int q = threadIdx.x; q < kMaskWords; q += blockDim.x) js.tmask[q] = s_in[q];
+    }
+    if (threadIdx.x == 0) js.n_tree_feats = n_tree;
+    __syncthreads();
+  }
+  for (int q = threadIdx.x; q < kMaskWords; q += blockDim.x) s_in[q] = js.tmask[q];
+  __syncthreads();
+  if (jp.collevel != 1.0f) {
+    int n_lvl = (int)(jp.collevel * (float)js.n_tree_feats); if (n_lvl < 1) n_lvl = 1;
+    sample_mask(stream_key(3u, (uint32_t)jp.fold, (uint32_t)round, (uint32_t)level), s_in, w.f, n_lvl, s_mask);
+    for (int q = threadIdx.x; q < kMaskWords; q += blockDim.x) js.lmask[q] = s_mask[q];
+  } else {
+    for (int q = threadIdx.x; q < kMaskWords; q += blockDim.x) js.lmask[q] = s_in[q];
+  }
+  if (threadIdx.x != 0) return;
+  // work items: histogram chunks of the nodes to build, (built, sibling) pairs to evaluate
+  Node* nodes = w.nodes + (size_t)j * kNodeCap;
+  HistItem* items = w.hitems + (size_t)j * w.hist_cap;
+  PairRec* pairs = w.pairs + (size_t)j * w.pair_cap;
+  int* zl = w.zlist + (size_t)j * w.hist_cap;
+  int ni = 0, np = 0, nz = 0;
+  unsigned long long rows_total = 0, built = 0;
+  if (level == 0) {
+    const Node& r = nodes[0];
+    int chunks = (int)((r.cnt + kHistRows - 1) / kHistRows); if (chunks < 1) chunks = 1;
+    for (int c = 0; c < chunks && ni < w.hist_cap; ++c) {
+      uint32_t b = (uint32_t)c * kHistRows;
+      uint32_t cnt = r.cnt > b ? (r.cnt - b < (uint32_t)kHistRows ? r.cnt - b : (uint32_t)kHistRows) : 0u;
+      items[ni++] = HistItem{0, b, cnt, (chunks > 1 ? 1 : 0) | (r.buf << 1)};
+    }
+    if (chunks > 1) zl[nz++] = 0;
+    pairs[np++] = PairRec{-1, 0};
+    rows_total += r.cnt; built += 1;
+  } else {
+    const int first = level_first(level - 1), last = level_first(level);
+    for (int p = first; p < last; ++p) {
+      if (nodes[p].state != kSplit) continue;
+      const int l = 2 * p + 1, r = 2 * p + 2;
+      const int bnode = nodes[l].cnt <= nodes[r].cnt ? l : r;
+      const Node& bn = nodes[bnode];
+      int chunks = (int)((bn.cnt + kHistRows - 1) / kHistRows); if (chunks < 1) chunks = 1;
+      for (int c = 0; c < chunks && ni < w.hist_cap; ++c) {
+        uint32_t b = (uint32_t)c * kHistRows;
+        uint32_t cnt = bn.cnt > b ? (bn.cnt - b < (uint32_t)kHistRows ? bn.cnt - b : (uint32_t)kHistRows) : 0u;
+        items[ni++] = HistItem{bnode, bn.begin + b, cnt, (chunks > 1 ? 1 : 0) | (bn.buf << 1)};
+      }
+      if (chunks > 1 && nz < w.hist_cap) zl[nz++] = bnode;
+      if (np < w.pair_cap) pairs[np++] = PairRec{p, bnode == r ? 1 : 0};
+      rows_total += bn.cnt; built += 1;
+    }
+  }
+  js.n_hist_items = ni; js.n_pairs = np; js.n_zero = nz;
+  if (rows_total) atomicAdd(&w.counters[0], rows_total);
+  if (built) atomicAdd(&w.counters[1], built);
+}
+
+__device__ __forceinline__ HistEntry* node_hist(const Wave& w, const JobParams& jp, int level, int node) {
+  return w.hist + ((level & 1) ? jp.hist_off[1] : jp.hist_off[0]) + (size_t)(node - level_first(level)) * w.groups * (kBins * kLanes);
+}
+
+__global__ void __launch_bounds__(256) k_hist_zero(Wave w, int level) {
+  const int j = blockIdx.y;
+  const JobState& js = w.js[j];
+  const JobParams jp = w.jp[j];
+  const int* zl = w.zlist + (size_t)j * w.hist_cap;
+  const int cells = w.groups * kBins * kLanes;
+  for (int z = blockIdx.x; z < js.n_zero; z += gridDim.x) {
+    longlong2* h = reinterpret_cast<longlong2*>(node_hist(w, jp, level, zl[z]));
+    for (int i = threadIdx.x; i < cells; i += blockDim.x) h[i] = make_longlong2(0, 0);
+  }
+}
+
+// ------------------------------------------------------------------ X5: histogram
+// One CTA = (job, work item, feature group of 32).  A warp takes 16 rows per step: lane = (row, 16-byte
+// half of the group's 32 bin bytes), loaded with one 128-bit read.  The 16 bytes are pre-rotated by the
+// row slot so that at unrolled step s the 32 lanes of a warp address 32 different features; with the
+// shared histogram laid out [bin][feature] the bank is the feature, so every ATOMS is conflict-free.
+__device__ __forceinline__ uint4 ld_stream(const uint4* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+
+__global__ void __launch_bounds__(kHistThreads) k_hist(Wave w, int level) {
+  const int j = blockIdx.y;
+  const JobState& js = w.js[j];
+  const int item_idx = blockIdx.x / w.groups, grp = blockIdx.x % w.groups;
+  if (item_idx >= js.n_hist_items) return;
+  const JobParams jp = w.jp[j];
+  const HistItem it = w.hitems[(size_t)j * w.hist_cap + item_idx];
+  extern __shared__ int sh[];
+  int* sh_g = sh;
+  int* sh_h = sh + kBins * kLanes;
+  for (int i = threadIdx.x; i < 2 * kBins * kLanes / 4; i += kHistThreads) reinterpret_cast<int4*>(sh)[i] = make_int4(0, 0, 0, 0);
+  __syncthreads();
+  const uint8_t* bins = w.folds[jp.fold].bins + (size_t)grp * kLanes;
+  const uint32_t* ridx = w.ridx + ((size_t)j * 2 + (size_t)((it.flags >> 1) & 1)) * w.nt_stride + it.begin;
+  const int2* gq = w.gq + (size_t)j * w.nt_stride;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int rl = lane >> 1, half = lane & 1;
+  const int q = rl >> 2, rb = (rl & 3) * 8;
+  const int fbase = half * 16;
+  const int nfeat_grp = min(kLanes, w.f - grp * kLanes);   // real features in this group
+  for (uint32_t base = (uint32_t)wid * 16u; base < it.cnt; base += (kHistThreads / 32) * 16u) {
+    const uint32_t p = base + (uint32_t)rl;
+    const bool valid = p < it.cnt;
+    uint32_t row = valid ? ridx[p] : 0u;
+    int2 g2 = valid ? gq[row] : make_int2(0, 0);
+    uint4 v = valid ? ld_stream(reinterpret_cast<const uint4*>(bins + (size_t)row * w.fpad + fbase)) : make_uint4(0, 0, 0, 0);
+    // rotate the 16 bytes right by rl bytes: word rotation by q, then funnel shift by rb bits
+    uint32_t u0 = q == 0 ? v.x : q == 1 ? v.y : q == 2 ? v.z : v.w;
+    uint32_t u1 = q == 0 ? v.y : q == 1 ? v.z : q == 2 ? v.w : v.x;
+    uint32_t u2 = q == 0 ? v.z : q == 1 ? v.w : q == 2 ? v.x : v.y;
+    uint32_t u3 = q == 0 ? v.w : q == 1 ? v.x : q == 2 ? v.y : v.z;
+    uint32_t r[4];
+    r[0] = __funnelshift_r(u0, u1, rb);
+    r[1] = __funnelshift_r(u1, u2, rb);
+    r[2] = __funnelshift_r(u2, u3, rb);
+    r[3] = __funnelshift_r(u3, u0, rb);
+#pragma unroll
+    for (int s = 0; s < 16; ++s) {
+      const uint32_t bin = (r[s >> 2] >> ((s & 3) * 8)) & 0xffu;
+      const int fl = fbase + ((s + rl) & 15);
+      if (valid && fl < nfeat_grp) {
+        const int a = (int)bin * kLanes + fl;
+        atomicAdd(&sh_g[a], g2.x);
+        atomicAdd(&sh_h[a], g2.y);
+      }
+    }
+  }
+  __syncthreads();
+  HistEntry* dst = node_hist(w, jp, level, it.node) + (size_t)grp * (kBins * kLanes);
+  if (it.flags & 1) {
+    for (int i = threadIdx.x; i < kBins * kLanes; i += kHistThreads) {
+      int g = sh_g[i], h = sh_h[i];
+      if (g) atomicAdd(reinterpret_cast<unsigned long long*>(&dst[i].g), (unsigned long long)(long long)g);
+      if (h) atomicAdd(reinterpret_cast<unsigned long long*>(&dst[i].h), (unsigned long long)(long long)h);
+    }
+  } else {
+    for (int i = threadIdx.x; i < kBins * kLanes; i += kHistThreads)
+      reinterpret_cast<longlong2*>(dst)[i] = make_longlong2((long long)sh_g[i], (long long)sh_h[i]);
+  }
+}
+
+// ------------------------------------------------------------------ X6: split enumeration
+// One CTA per (job, parent): warps = 2 children x feature groups, lane = feature.  Each lane keeps a
+// running prefix over its feature's bins (EnumerateSplit<+1>), the sibling histogram is formed on the
+// fly as parent - built, and the per-lane best candidates are merged with warp shuffles.
+struct Cand { float chg; int f; int b; long long GL, HL; };
+
+__device__ __forceinline__ bool better(float chg, int f, float ochg, int of) {
+  // SplitEntry::NeedReplace with ascending feature order: strictly greater, ties keep the lower feature
+  return (chg > ochg) || (chg == ochg && f >= 0 && (of < 0 || f < of));
+}
+
+__global__ void k_scan(Wave w, int level) {
+  const int j = blockIdx.y;
+  const JobState& js = w.js[j];
+  if ((int)blockIdx.x >= js.n_pairs) return;
+  const JobParams jp = w.jp[j];
+  const PairRec pr = w.pairs[(size_t)j * w.pair_cap + blockIdx.x];
+  const int G = w.groups;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int c = warp / G, grp = warp % G;
+  Node* nodes = w.nodes + (size_t)j * kNodeCap;
+  TreeNode* tree = w.tree + (size_t)j * kNodeCap;
+  const bool live = (level > 0) || (c == 0);
+  const int node = level == 0 ? 0 : 2 * pr.parent + 1 + c;
+  const bool is_built = (level == 0) || (c == pr.build_right);
+  const int built_node = level == 0 ? 0 : 2 * pr.parent + 1 + pr.build_right;
+  const FoldDev fd = w.folds[jp.fold];
+  const int f = grp * kLanes + lane;
+  const int nc = f < w.f ? fd.ncuts[f] : 0;
+  const bool factive = f < w.f && ((js.lmask[f >> 5] >> (f & 31)) & 1u);
+  const int maxnc = w.grp_maxnc[jp.fold * G + grp];
+  const bool write_sib = live && !is_built && (level + 1 < jp.max_depth);
+  const size_t goff = (size_t)grp * (kBins * kLanes) + lane;
+  const longlong2* hbuilt = reinterpret_cast<const longlong2*>(node_hist(w, jp, level, built_node)) + goff;
+  const longlong2* hpar = level > 0 ? reinterpret_cast<const longlong2*>(node_hist(w, jp, level - 1, pr.parent)) + goff : nullptr;
+  longlong2* hown = reinterpret_cast<longlong2*>(node_hist(w, jp, level, node)) + goff;
+  const long long Gt = nodes[node].G, Ht = nodes[node].H;
+  const double inv_sg = js.inv_sg, inv_sh = js.inv_sh;
+  float root_gain = nodes[node].root_gain;
+  if (level == 0) root_gain = calc_gain(jp, (double)Gt * inv_sg, (double)Ht * inv_sh);
+  Cand best{0.0f, -1, -1, 0, 0};
+  if (live) {
+    long long GL = 0, HL = 0;
+#pragma unroll 4
+    for (int b = 0; b < maxnc; ++b) {
+      longlong2 e = hbuilt[(size_t)b * kLanes];
+      if (!is_built) {
+        longlong2 pe = hpar[(size_t)b * kLanes];
+        e.x = pe.x - e.x; e.y = pe.y - e.y;
+        if (write_sib) hown[(size_t)b * kLanes] = e;
+      }
+      GL += e.x; HL += e.y;
+      if (factive && b < nc && (e.x != 0 || e.y != 0)) {
+        double gl = (double)GL * inv_sg, hl = (double)HL * inv_sh;
+        double gr = (double)(Gt - GL) * inv_sg, hr = (double)(Ht - HL) * inv_sh;
+        if (hl >= jp.mcw && hr >= jp.mcw) {
+          float chg = split_gain(jp, gl, hl, gr, hr) - root_gain;
+          if (!isinf(chg) && chg > best.chg) { best.chg = chg; best.f = f; best.b = b; best.GL = GL; best.HL = HL; }
+        }
+      }
+    }
+  }
+  for (int d = 16; d; d >>= 1) {
+    float ochg = __shfl_xor_sync(0xffffffffu, best.chg, d);
+    int of = __shfl_xor_sync(0xffffffffu, best.f, d);
+    int ob = __shfl_xor_sync(0xffffffffu, best.b, d);
+    long long oGL = __shfl_xor_sync(0xffffffffu, best.GL, d);
+    long long oHL = __shfl_xor_sync(0xffffffffu, best.HL, d);
+    if (better(ochg, of, best.chg, best.f)) { best.chg = ochg; best.f = of; best.b = ob; best.GL = oGL; best.HL = oHL; }
+  }
+  __shared__ Cand s_c[16];
+  if (lane == 0) s_c[warp] = best;
+  __syncthreads();
+  if (!(lane == 0 && grp == 0 && live)) return;
+  for (int g2 = 1; g2 < G; ++g2) {
+    const Cand o = s_c[c * G + g2];
+    if (better(o.chg, o.f, best.chg, best.f)) best = o;
+  }
+  Node& nd = nodes[node];
+  if (level == 0) {
+    nd.root_gain = root_gain;
+    nd.leaf = jp.eta * calc_weight(jp, (double)Gt * inv_sg, (double)Ht * inv_sh);
+  }
+  bool valid = best.f >= 0 && best.chg > kRtEps;   // CPUExpandEntry::IsValid
+  if (valid) {
+    double hl = (double)best.HL * inv_sh, hr = (double)(Ht - best.HL) * inv_sh;
+    if (hl == 0.0 || hr == 0.0) valid = false;
+    if (best.chg < jp.gamma) valid = false;
+  }
+  nd.loss_chg = best.chg;
+  if (!valid) {
+    nd.state = kLeaf;
+    tree[node] = TreeNode{nd.leaf, (int16_t)-1, (uint8_t)0, (uint8_t)kLeaf};
+    return;
+  }
+  nd.state = kSplit; nd.feat = (int16_t)best.f; nd.bin = (uint8_t)best.b;
+  tree[node] = TreeNode{0.f, (int16_t)best.f, (uint8_t)best.b, (uint8_t)kSplit};
+  const uint8_t child_state = (level + 1 < jp.max_depth) ? kOpen : kLeaf;   // Driver::IsChildValid
+  const long long cg[2] = {best.GL, Gt - best.GL}, chh[2] = {best.HL, Ht - best.HL};
+  for (int s = 0; s < 2; ++s) {
+    Node& ch = nodes[2 * node + 1 + s];
+    double g = (double)cg[s] * inv_sg, h = (double)chh[s] * inv_sh;
+    ch.G = cg[s]; ch.H = chh[s];
+    ch.leaf = jp.eta * calc_weight(jp, g, h);
+    ch.root_gain = calc_gain(jp, g, h);
+    ch.loss_chg = 0.f; ch.feat = -1; ch.bin = 0; ch.state = child_state;
+    ch.begin = 0; ch.cnt = 0; ch.buf = 0;
+    tree[2 * node + 1 + s] = TreeNode{ch.leaf, (int16_t)-1, (uint8_t)0, child_state};
+  }
+}
+
+// ------------------------------------------------------------------ X7: stable row partition
+__global__ void k_plan_part(Wave w, int level) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= w.n_jobs) return;
+  JobState& js = w.js[j];
+  const JobParams jp = w.jp[j];
+  js.n_part_items = 0;
+  if (!js.active || level + 1 >= jp.max_depth) return;
+  const Node* nodes = w.nodes + (size_t)j * kNodeCap;
+  PartItem* items = w.pitems + (size_t)j * w.part_cap;
+  int ni = 0;
+  const int first = level_first(level), last = level_first(level + 1);
+  for (int nidx = first; nidx < last; ++nidx) {
+    const Node& nd = nodes[nidx];
+    if (nd.state != kSplit) continue;
+    int chunks = (int)((nd.cnt + kPartRows - 1) / kPartRows);
+    const int first_item = ni;
+    for (int c = 0; c < chunks && ni < w.part_cap; ++c) {
+      uint32_t b = (uint32_t)c * kPartRows;
+      uint32_t cnt = nd.cnt - b < (uint32_t)kPartRows ? nd.cnt - b : (uint32_t)kPartRows;
+      items[ni++] = PartItem{nidx, nd.begin + b, cnt, first_item, chunks, nd.begin, nd.cnt, (int)nd.buf};
+    }
+  }
+  js.n_part_items = ni;
+}
+
+__global__ void __launch_bounds__(256) k_part_count(Wave w, int level) {
+  const int j = blockIdx.y;
+  const JobState& js = w.js[j];
+  if ((int)blockIdx.x >= js.n_part_items) return;
+  const JobParams jp = w.jp[j];
+  const PartItem it = w.pitems[(size_t)j * w.part_cap + blockIdx.x];
+  const Node& nd = w.nodes[(size_t)j * kNodeCap + it.node];
+  const int feat = nd.feat; const uint32_t sbin = nd.bin;
+  const uint8_t* bins = w.folds[jp.fold].bins + feat;
+  const uint32_t* src = w.ridx + ((size_t)j * 2 + it.buf) * w.nt_stride + it.begin;
+  uint32_t* bits = w.pbits + ((size_t)j * w.part_cap + blockIdx.x) * (kPartRows / 32);
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  int cnt = 0;
+#pragma unroll
+  for (int t = 0; t < kPartRows / 256; ++t) {
+    const uint32_t p = (uint32_t)t * 256u + threadIdx.x;
+    bool left = false;
+    if (p < it.cnt) { uint32_t row = src[p]; left = (uint32_t)bins[(size_t)row * w.fpad] <= sbin; }
+    uint32_t m = __ballot_sync(0xffffffffu, left);
+    if (lane == 0) { bits[t * 8 + wid] = m; cnt += __popc(m); }
+  }
+  __shared__ int s_cnt[8];
+  if (lane == 0) s_cnt[wid] = cnt;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int tot = 0;
+    for (int q = 0; q < 8; ++q) tot += s_cnt[q];
+    w.pleft[(size_t)j * w.part_cap + blockIdx.x] = tot;
+  }
+}
+
+__global__ void __launch_bounds__(256) k_part_scatter(Wave w, int level) {
+  const int j = blockIdx.y;
+  const JobState& js = w.js[j];
+  if ((int)blockIdx.x >= js.n_part_items) return;
+  const PartItem it = w.pitems[(size_t)j * w.part_cap + blockIdx.x];
+  const int* pleft = w.pleft + (size_t)j * w.part_cap;
+  const uint32_t* bits = w.pbits + ((size_t)j * w.part_cap + blockIdx.x) * (kPartRows / 32);
+  const uint32_t* src = w.ridx + ((size_t)j * 2 + it.buf) * w.nt_stride;
+  uint32_t* dst = w.ridx + ((size_t)j * 2 + (it.buf ^ 1)) * w.nt_stride;
+  __shared__ int s_pref[kPartRows / 32];
+  __shared__ int s_red[2][8];
+  __shared__ int s_prev, s_total;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  int prevL = 0, totL = 0;
+  for (int i = it.first_item + threadIdx.x; i < it.first_item + it.n_items; i += blockDim.x) {
+    int v = pleft[i];
+    totL += v;
+    if (i < (int)blockIdx.x) prevL += v;
+  }
+  for (int d = 16; d; d >>= 1) { prevL += __shfl_xor_sync(0xffffffffu, prevL, d); totL += __shfl_xor_sync(0xffffffffu, totL, d); }
+  if (lane == 0) { s_red[0][wid] = prevL; s_red[1][wid] = totL; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int a = 0, b = 0;
+    for (int q2 = 0; q2 < 8; ++q2) { a += s_red[0][q2]; b += s_red[1][q2]; }
+    s_prev = a; s_total = b;
+    int run = 0;
+    for (int q2 = 0; q2 < kPartRows / 32; ++q2) { s_pref[q2] = run; run += __popc(bits[q2]); }
+  }
+  __syncthreads();
+  prevL = s_prev; totL = s_total;
+  const uint32_t rel0 = it.begin - it.node_begin;
+#pragma unroll
+  for (int t = 0; t < kPartRows / 256; ++t) {
+    const uint32_t p = (uint32_t)t * 256u + threadIdx.x;
+    if (p < it.cnt) {
+      const uint32_t word = bits[t * 8 + wid];
+      const uint32_t row = src[it.begin + p];
+      const int lrank = s_pref[t * 8 + wid] + __popc(word & ((1u << lane) - 1u));
+      const bool left = (word >> lane) & 1u;
+      const uint32_t rel = rel0 + p;
+      const uint32_t d = left ? it.node_begin + (uint32_t)(prevL + lrank)
+                              : it.node_begin + (uint32_t)totL + (rel - (uint32_t)(prevL + lrank));
+      dst[d] = row;
+    }
+  }
+  if ((int)blockIdx.x == it.first_item && threadIdx.x == 0) {
+    Node* nodes = w.nodes + (size_t)j * kNodeCap;
+    Node& L = nodes[2 * it.node + 1];
+    Node& R = nodes[2 * it.node + 2];
+    L.begin = it.node_begin; L.cnt = (uint32_t)totL; L.buf = (uint8_t)(it.buf ^ 1);
+    R.begin = it.node_begin + (uint32_t)totL; R.cnt = it.node_cnt - (uint32_t)totL; R.buf = (uint8_t)(it.buf ^ 1);
+  }
+}
+
+// ------------------------------------------------------------------ X8 + X9: prediction update and metric
+// Every row (train slice and test slice) walks the new tree on its bin bytes (bin <= split bin  <=>
+// raw value < threshold); the prediction is updated in place, test rows add their
+// metric term, train rows record the gradient range of the next round.
+__global__ void __launch_bounds__(256) k_predict(Wave w) {
+  const int j = blockIdx.y;
+  const JobState& js = w.js[j];
+  if (!js.active) return;
+  const JobParams jp = w.jp[j];
+  const FoldDev fd = w.folds[jp.fold];
+  __shared__ TreeNode s_tree[kNodeCap];
+  const int n_nodes = (2 << jp.max_depth) - 1;
+  const TreeNode* tree = w.tree + (size_t)j * kNodeCap;
+  for (int i = threadIdx.x; i < n_nodes; i += blockDim.x) s_tree[i] = tree[i];
+  __syncthreads();
+  float* pred = w.pred + (size_t)j * w.n;
+  const long long r0 = (long long)blockIdx.x * kPredRows;
+  float gm = 0.f, hm = 0.f;
+  double msum = 0.0;
+  for (int i = threadIdx.x; i < kPredRows; i += blockDim.x) {
+    const long long r = r0 + i;
+    if (r >= w.n) break;
+    const uint8_t* row = fd.bins + (size_t)r * w.fpad;
+    int nid = 0;
+    TreeNode t = s_tree[0];
+    while (t.state == kSplit) {
+      nid = 2 * nid + 1 + (row[t.feat] > t.bin ? 1 : 0);
+      t = s_tree[nid];
+    }
+    const float p = pred[r] + t.leaf;
+    pred[r] = p;
+    const float y = fd.y[r];
+    if (r < fd.ntrain) {
+      float g, h;
+      grad_pair(w.objective, p, y, jp.spw, g, h);
+      gm = fmaxf(gm, fabsf(g)); hm = fmaxf(hm, fabsf(h));
+    } else {
+      const float pv = w.objective == 1 ? sigmoid_x(p) : p;
+      float e;
+      if (w.metric == 1) {     // EvalRowLogLoss
+        const float eps = 1e-16f, pneg = 1.0f - pv;
+        if (pv < eps) e = -y * logf(eps) - (1.0f - y) * logf(1.0f - eps);
+        else if (pneg < eps) e = -y * logf(1.0f - eps) - (1.0f - y) * logf(eps);
+        else e = -y * logf(pv) - (1.0f - y) * logf(pneg);
+      } else {                 // EvalRowRMSE
+        const float d = y - pv;
+        e = d * d;
+      }
+      msum += (double)e;
+    }
+  }
+  for (int d = 16; d; d >>= 1) {
+    gm = fmaxf(gm, __shfl_xor_sync(0xffffffffu, gm, d));
+    hm = fmaxf(hm, __shfl_xor_sync(0xffffffffu, hm, d));
+    msum += __shfl_xor_sync(0xffffffffu, msum, d);
+  }
+  __shared__ double s_m[8];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (lane == 0) {
+    if (gm > 0.f) atomicMax(&w.js[j].gmax_bits, __float_as_uint(gm));
+    if (hm > 0.f) atomicMax(&w.js[j].hmax_bits, __float_as_uint(hm));
+    s_m[wid] = msum;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0;
+    for (int q = 0; q < 8; ++q) t += s_m[q];
+    w.mpart[(size_t)j * w.pred_chunks + blockIdx.x] = t;
+  }
+}
+
+// aggcv mean over folds, EarlyStopping on the test mean (minimise, strict improvement), next-round set-up
+__global__ void __launch_bounds__(32) k_round_end(Wave w, int first, double* fitness_out, int* rounds_out) {
+  const int i = blockIdx.x;
+  IndState& is = w.is[i];
+  if (!is.active) return;
+  const int lane = threadIdx.x;
+  if (!first) {
+    double fold_sum = 0.0;
+    for (int k = 0; k < w.nfold; ++k) {
+      const int j = i * w.nfold + k;
+      const double* mp = w.mpart + (size_t)j * w.pred_chunks;
+      double s = 0.0;
+      for (int c = lane; c < w.pred_chunks; c += 32) s += mp[c];
+      for (int d = 16; d; d >>= 1) s += __shfl_xor_sync(0xffffffffu, s, d);
+      const double nt = (double)w.folds[w.jp[j].fold].ntest;
+      fold_sum += (w.metric == 0) ? sqrt(s / nt) : s / nt;
+    }
+    const double mean = fold_sum / (double)w.nfold;
+    bool done = false;
+    if (lane == 0) {
+      const int it = is.round;
+      if (w.trace) w.trace[(size_t)i * w.num_boost_round + it] = mean;
+      is.last_mean = mean;
+      is.rounds_run = it + 1;
+      if (w.early_stopping_rounds > 0) {
+        if (it == 0) { is.best_score = mean; is.best_iter = 0; }
+        else if (mean < is.best_score) { is.best_score = mean; is.best_iter = it; }
+        else if (it - is.best_iter >= w.early_stopping_rounds) { is.stopped = 1; }
+      }
+      is.round = it + 1;
+      if (is.stopped || is.round >= w.num_boost_round) {
+        is.active = 0;
+        is.fitness = is.stopped ? is.best_score : is.last_mean;   // cv() truncates to best_iteration + 1 rows
+        fitness_out[is.out_index] = is.fitness;
+        if (rounds_out) rounds_out[is.out_index] = is.rounds_run;
+        for (int k = 0; k < w.nfold; ++k) w.js[i * w.nfold + k].active = 0;
+        atomicAdd(&w.counters[2], (unsigned long long)(-1ll));
+        done = true;
+      }
+    }
+    done = __shfl_sync(0xffffffffu, (int)done, 0);
+    if (done) return;
+  }
+  if (lane < w.nfold) prepare_next_round(w, i * w.nfold + lane);
+}
+
+// parity dumps
+__global__ void k_dump_trees(Wave w, int round, int tree_rounds, gt_tree_node* out) {
+  const int j = blockIdx.y;
+  const Node* nodes = w.nodes + (size_t)j * kNodeCap;
+  gt_tree_node* o = out + ((size_t)j * tree_rounds + round) * (kNodeCap - 1);
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < kNodeCap - 1; i += gridDim.x * blockDim.x) {
+    const Node& nd = nodes[i];
+    gt_tree_node r;
+    if (nd.state == kSplit) { r.feat = nd.feat; r.bin = nd.bin; r.value = 0.f; r.gain = nd.loss_chg; }
+    else if (nd.state == kLeaf) { r.feat = -1; r.bin = 0; r.value = nd.leaf; r.gain = 0.f; }
+    else { r.feat = -2; r.bin = 0; r.value = 0.f; r.gain = 0.f; }
+    o[i] = r;
+  }
+}
+
+__global__ void k_dump_node_rows(Wave w, gt_node_rows* out) {
+  const int j = blockIdx.y;
+  const Node* nodes = w.nodes + (size_t)j * kNodeCap;
+  gt_node_rows* o = out + (size_t)j * (kNodeCap - 1);
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < kNodeCap - 1; i += gridDim.x * blockDim.x) {
+    const Node& nd = nodes[i];
+    o[i] = gt_node_rows{nd.begin, nd.cnt, (int)nd.buf, (int)nd.state};
+  }
+}
+
+}  // namespace
+
+int hist_smem_bytes() { return kHistSmem; }
+
+int configure_kernels() {
+  return (int)cudaFuncSetAttribute(k_hist, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmem);
+}
+
+void launch_init_wave(const Wave& w, cudaStream_t s) {
+  k_init_wave<<<dim3(w.pred_chunks, w.n_jobs), 256, 0, s>>>(w);
+}
+void launch_grad(const Wave& w, cudaStream_t s) {
+  int chunks = (int)((w.nt_stride + kPredRows - 1) / kPredRows);
+  k_grad<<<dim3(chunks, w.n_jobs), 256, 0, s>>>(w);
+}
+void launch_plan_hist(const Wave& w, int level, cudaStream_t s) { k_plan_hist<<<w.n_jobs, 256, 0, s>>>(w, level); }
+void launch_hist_zero(const Wave& w, int level, cudaStream_t s) { k_hist_zero<<<dim3(32, w.n_jobs), 256, 0, s>>>(w, level); }
+void launch_hist(const Wave& w, int level, cudaStream_t s) {
+  int cap = hist_items_bound(w, level);
+  k_hist<<<dim3(cap * w.groups, w.n_jobs), kHistThreads, kHistSmem, s>>>(w, level);
+}
+void launch_scan(const Wave& w, int level, cudaStream_t s) {
+  int pairs = level == 0 ? 1 : (1 << (level - 1));
+  k_scan<<<dim3(pairs, w.n_jobs), 2 * w.groups * 32, 0, s>>>(w, level);
+}
+void launch_plan_part(const Wave& w, int level, cudaStream_t s) { k_plan_part<<<(w.n_jobs + 63) / 64, 64, 0, s>>>(w, level); }
+void launch_part_count(const Wave& w, int level, cudaStream_t s) {
+  k_part_count<<<dim3(part_items_bound(w, level), w.n_jobs), 256, 0, s>>>(w, level);
+}
+void launch_part_scatter(const Wave& w, int level, cudaStream_t s) {
+  k_part_scatter<<<dim3(part_items_bound(w, level), w.n_jobs), 256, 0, s>>>(w, level);
+}
+void launch_predict(const Wave& w, cudaStream_t s) { k_predict<<<dim3(w.pred_chunks, w.n_jobs), 256, 0, s>>>(w); }
+void launch_round_end(const Wave& w, int first, double* fitness_out, int* rounds_out, cudaStream_t s) {
+  k_round_end<<<w.n_inds, 32, 0, s>>>(w, first, fitness_out, rounds_out);
+}
+void launch_dump_trees(const Wave& w, int round, int tree_rounds, gt_tree_node* out, cudaStream_t s) {
+  k_dump_trees<<<dim3(2, w.n_jobs), 256, 0, s>>>(w, round, tree_rounds, out);
+}
+void launch_dump_node_rows(const Wave& w, gt_node_rows* out, cudaStream_t s) {
+  k_dump_node_rows<<<dim3(2, w.n_jobs), 256, 0, s>>>(w, out);
+}
+
+}  // namespace gt

@@ -1,0 +1,129 @@
+// Shared device-side types of the gentun_b200 engine (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace gt {
+
+constexpr int kBins = 256;          // max_bin (xgboost default, never overridden by gentun)
+constexpr int kLanes = 32;          // features per histogram group == smem banks
+constexpr int kMaxDepth = 10;       // max_depth gene range 3..10 (gentun/individuals.py:167)
+constexpr int kNodeCap = 2048;      // heap slots per tree (2^(10+1)-1 used)
+constexpr int kHistRows = 2048;     // rows per histogram work item (bounds int32 partial sums)
+constexpr int kPartRows = 2048;     // rows per partition work item
+constexpr int kQuantBits = 19;      // |quantised gradient| <= 2^19  (2^19 * 2048 = 2^30 < 2^31)
+constexpr int kPredRows = 2048;     // rows per predict CTA
+constexpr int kMaskWords = 8;       // feature masks: up to 256 features
+
+enum NodeState : uint8_t { kAbsent = 0, kOpen = 1, kSplit = 2, kLeaf = 3 };
+
+struct HistEntry { long long g, h; };   // fixed-point sums, one (feature, bin) cell, 16 B
+
+struct Node {          // working record of one heap slot
+  long long G, H;      // quantised gradient / hessian sums of the node
+  uint32_t begin, cnt; // segment of row-set buffer `buf`
+  float leaf;          // eta * weight
+  float root_gain;     // CalcGain(G, H)
+  float loss_chg;
+  int16_t feat;
+  uint8_t bin;
+  uint8_t state;
+  uint8_t buf;
+  uint8_t pad[3];
+};
+
+struct TreeNode {      // compact record read by the prediction kernel, 8 B
+  float leaf;
+  int16_t feat;
+  uint8_t bin;
+  uint8_t state;
+};
+
+struct HistItem { int node; uint32_t begin; uint32_t cnt; int flags; };  // flags bit0: shared (atomic flush), bit1: buf
+struct PairRec { int parent; int build_right; };
+struct PartItem { int node; uint32_t begin; uint32_t cnt; int first_item; int n_items; uint32_t node_begin; uint32_t node_cnt; int buf; };
+
+struct JobParams {     // constant over one evaluation
+  float eta, mcw, gamma, mds, subsample, coltree, collevel, lambda, alpha, spw;
+  float base_margin;
+  int max_depth;
+  int fold;
+  int ind;             // index inside the wave
+  unsigned long long hist_off[2];   // element offsets of the even / odd level histogram buffers
+};
+
+struct JobState {
+  int active;
+  int n_hist_items, n_pairs, n_part_items, n_zero;
+  unsigned gmax_bits, hmax_bits;    // float bit patterns, atomicMax'ed
+  float sg, sh;                     // quantisation scales (powers of two)
+  double inv_sg, inv_sh;
+  uint32_t tmask[kMaskWords];       // colsample_bytree set of the current tree
+  uint32_t lmask[kMaskWords];       // colsample_bylevel set of the current level
+  int n_tree_feats;
+};
+
+struct IndState {
+  int active;
+  int round;          // next round to train
+  int best_iter;
+  int stopped;
+  double best_score;
+  double last_mean;
+  double fitness;
+  int rounds_run;
+  int out_index;      // position in the caller's arrays
+};
+
+struct FoldDev {
+  const uint8_t* bins;   // [n][fpad] fold order (train slice rows then test slice rows)
+  const float* y;        // [n] fold order
+  const float* cuts;     // [f][256]
+  const int* ncuts;      // [f]
+  long long ntrain, ntest;
+};
+
+struct Wave {            // passed by value to kernels
+  int n_jobs, n_inds, nfold;
+  long long n;           // rows
+  long long nt_stride;   // row-set stride (>= max ntrain, multiple of 32)
+  int f, fpad, groups;
+  int objective, metric, num_boost_round, early_stopping_rounds;
+  int hist_cap, pair_cap, part_cap;  // per-job record capacities
+  int pred_chunks;
+  const FoldDev* folds;
+  const int* grp_maxnc;  // [nfold][groups] max ncuts inside the group
+  JobParams* jp;
+  JobState* js;
+  IndState* is;
+  Node* nodes;           // [n_jobs][kNodeCap]
+  TreeNode* tree;        // [n_jobs][kNodeCap]
+  float* pred;           // [n_jobs][n]
+  int2* gq;              // [n_jobs][nt_stride]
+  uint32_t* ridx;        // [n_jobs][2][nt_stride]
+  HistEntry* hist;       // arena
+  HistItem* hitems;      // [n_jobs][hist_cap]
+  int* zlist;            // [n_jobs][hist_cap] nodes whose histogram must be cleared
+  PairRec* pairs;        // [n_jobs][pair_cap]
+  PartItem* pitems;      // [n_jobs][part_cap]
+  uint32_t* pbits;       // [n_jobs][part_cap][kPartRows/32]
+  int* pleft;            // [n_jobs][part_cap]
+  double* mpart;         // [n_jobs][pred_chunks] per-CTA metric partial sums
+  double* trace;         // [n_inds][num_boost_round] or null
+  unsigned long long* counters;  // [0] rows through hist, [1] node histograms built, [2] active individuals
+};
+
+// counter-based generator (definition shared with the oracle by specification)
+__host__ __device__ inline uint64_t mix64(uint64_t z) {
+  z += 0x9e3779b97f4a7c15ull;
+  z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
+  z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
+  return z ^ (z >> 31);
+}
+__host__ __device__ inline uint64_t stream_key(uint32_t tag, uint32_t fold, uint32_t round, uint32_t level) {
+  return mix64(((uint64_t)tag << 60) ^ ((uint64_t)fold << 48) ^ ((uint64_t)level << 40) ^ (uint64_t)round);
+}
+__host__ __device__ inline uint64_t draw64(uint64_t key, uint64_t index) { return mix64(key ^ (index * 0xd1342543de82ef95ull)); }
+__host__ __device__ inline float u01(uint64_t h) { return (float)(h >> 40) * (1.0f / 16777216.0f); }
+
+}  // namespace gt

@@ -1,0 +1,691 @@
+// Host side of the engine and its C ABI (include/gentun_b200.h).
+//
+// Stands where XgboostModel.cross_validate (/root/reference/gentun/models/xgboost_models.py:28-37)
+// calls into xgboost: gt_engine_create ~ xgb.DMatrix (:32), gt_engine_eval ~ xgb.cv (:33-36) + the
+// 'test-<metric>-mean' last-row read (:37), for a whole batch of gene sets
+// (Population.get_fittest, gentun/populations.py:55-58, evaluates them one by one).
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../../include/gentun_b200.h"
+#include "common.cuh"
+#include "kernels.h"
+
+namespace {
+
+thread_local std::string g_err = "";
+
+int fail(int code, const char* fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+
+#define GT_CUDA(expr)                                                                          \
+  do {                                                                                         \
+    cudaError_t e__ = (expr);                                                                  \
+    if (e__ != cudaSuccess) return fail(GT_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__); \
+  } while (0)
+
+// ---- numpy legacy RandomState stream (np.random.seed(s); np.random.permutation(n)), as used by
+// xgboost training.py mknfold.  MT19937 + masked-rejection interval + Fisher-Yates from the top.
+struct Mt19937 {
+  uint32_t s[624];
+  int at;
+  explicit Mt19937(uint32_t seed) {
+    for (int i = 0; i < 624; ++i) { s[i] = seed; seed = 1812433253u * (seed ^ (seed >> 30)) + (uint32_t)(i + 1); }
+    at = 624;
+  }
+  void refill() {
+    for (int k = 0; k < 624; ++k) {
+      uint32_t y = (s[k] & 0x80000000u) | (s[(k + 1) % 624] & 0x7fffffffu);
+      s[k] = s[(k + 397) % 624] ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+    }
+    at = 0;
+  }
+  uint32_t next() {
+    if (at == 624) refill();
+    uint32_t y = s[at++];
+    y ^= y >> 11; y ^= (y << 7) & 0x9d2c5680u; y ^= (y << 15) & 0xefc60000u; y ^= y >> 18;
+    return y;
+  }
+  uint64_t below_or_equal(uint64_t top) {
+    if (top == 0) return 0;
+    uint64_t mask = top;
+    for (int sh = 1; sh <= 32; sh <<= 1) mask |= mask >> sh;
+    uint64_t v;
+    if (top <= 0xffffffffull) {
+      do { v = next() & mask; } while (v > top);
+    } else {
+      do { uint64_t hi = next(); uint64_t lo = next(); v = ((hi << 32) | lo) & mask; } while (v > top);
+    }
+    return v;
+  }
+};
+
+void make_folds_host(int64_t n, int32_t nfold, uint32_t seed, int64_t* perm, int64_t* fold_begin) {
+  Mt19937 rng(seed);
+  for (int64_t i = 0; i < n; ++i) perm[i] = i;
+  for (int64_t i = n - 1; i > 0; --i) std::swap(perm[i], perm[(int64_t)rng.below_or_equal((uint64_t)i)]);
+  int64_t q = n / nfold, r = n % nfold, at = 0;   // np.array_split
+  for (int k = 0; k < nfold; ++k) { fold_begin[k] = at; at += q + (k < r ? 1 : 0); }
+  fold_begin[nfold] = at;
+}
+
+template <typename T>
+struct DevBuf {
+  T* p = nullptr;
+  size_t count = 0;
+  ~DevBuf() { release(); }
+  void release() { if (p) cudaFree(p); p = nullptr; count = 0; }
+  cudaError_t ensure(size_t c) {
+    if (c <= count && p) return cudaSuccess;
+    release();
+    cudaError_t e = cudaMalloc(&p, std::max<size_t>(c, 1) * sizeof(T));
+    if (e == cudaSuccess) count = c;
+    return e;
+  }
+};
+
+struct FoldSet {
+  int nfold = 0;
+  std::vector<int64_t> perm, fold_begin;
+  std::vector<int64_t> ntrain, ntest;
+  std::vector<std::vector<uint32_t>> rows;   // fold order: train slice then test slice
+  std::vector<DevBuf<uint32_t>> d_rows;
+  std::vector<DevBuf<uint8_t>> d_bins;
+  std::vector<DevBuf<float>> d_y;
+  DevBuf<float> d_cuts;                       // [nfold][f][256]
+  DevBuf<int> d_ncuts;                        // [nfold][f]
+  DevBuf<gt::FoldDev> d_folds;
+  DevBuf<int> d_grp_maxnc;
+  std::vector<int> h_ncuts;
+  // label statistics of each train slice for the base-score stump (FitIntercept::InitEstimation)
+  std::vector<double> sum_not1_sq, sum_not1_lg;   // sum over labels != 1 of (0 - y) / (0.5 - y)
+  std::vector<int64_t> n1, nnot1;
+  double prepare_ms = 0;
+};
+
+}  // namespace
+
+struct gt_engine {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  int64_t n = 0, ldx = 0;
+  int f = 0, fpad = 0, groups = 0;
+  const float* d_X = nullptr;
+  const float* d_y = nullptr;
+  DevBuf<float> own_X, own_y;
+  std::vector<float> h_y;
+  int64_t mem_budget = 0;
+  int collect_timing = 0;
+  std::map<int, std::unique_ptr<FoldSet>> foldsets;
+  gt_stats stats{};
+};
+
+namespace {
+
+void limit_size_level(size_t maxn, double eps, size_t* nlevel, size_t* limit) {   // quantile.h LimitSizeLevel
+  *nlevel = 1;
+  for (;;) {
+    *limit = (size_t)std::ceil((double)*nlevel / eps) + 1;
+    *limit = std::min(maxn, *limit);
+    if (((size_t)1 << *nlevel) * *limit >= maxn) break;
+    ++*nlevel;
+  }
+}
+
+int prepare_impl(gt_engine* e, int nfold, FoldSet** out) {
+  auto it = e->foldsets.find(nfold);
+  if (it != e->foldsets.end()) { *out = it->second.get(); return GT_OK; }
+  if (nfold < 2 || nfold > 32 || nfold > e->n) return fail(GT_ERR_ARG, "nfold=%d out of range for n=%lld", nfold, (long long)e->n);
+  GT_CUDA(cudaSetDevice(e->device));
+  std::unique_ptr<FoldSet> fs(new FoldSet());
+  fs->nfold = nfold;
+  const int64_t n = e->n;
+  const int f = e->f;
+  fs->perm.resize(n); fs->fold_begin.resize(nfold + 1);
+  make_folds_host(n, nfold, 0u, fs->perm.data(), fs->fold_begin.data());
+  fs->ntrain.resize(nfold); fs->ntest.resize(nfold); fs->rows.resize(nfold);
+  fs->d_rows.resize(nfold); fs->d_bins.resize(nfold); fs->d_y.resize(nfold);
+  fs->sum_not1_sq.assign(nfold, 0); fs->sum_not1_lg.assign(nfold, 0); fs->n1.assign(nfold, 0); fs->nnot1.assign(nfold, 0);
+  cudaEvent_t ev0, ev1;
+  GT_CUDA(cudaEventCreate(&ev0)); GT_CUDA(cudaEventCreate(&ev1));
+  GT_CUDA(cudaEventRecord(ev0, e->stream));
+  std::vector<const uint32_t*> h_row_ptrs(nfold);
+  std::vector<long long> h_ntrain(nfold);
+  std::vector<int> h_limit(nfold);
+  size_t lmax = 1, nlevel_max = 1;
+  for (int k = 0; k < nfold; ++k) {
+    int64_t nt = fs->fold_begin[k + 1] - fs->fold_begin[k];
+    fs->ntest[k] = nt; fs->ntrain[k] = n - nt;
+    auto& rows = fs->rows[k];
+    rows.resize(n);
+    size_t o = 0;   // DMatrix.slice(np.concatenate(other chunks)) then the test chunk
+    for (int c = 0; c < nfold; ++c) {
+      if (c == k) continue;
+      for (int64_t q = fs->fold_begin[c]; q < fs->fold_begin[c + 1]; ++q) rows[o++] = (uint32_t)fs->perm[q];
+    }
+    for (int64_t q = fs->fold_begin[k]; q < fs->fold_begin[k + 1]; ++q) rows[o++] = (uint32_t)fs->perm[q];
+    GT_CUDA(fs->d_rows[k].ensure(n));
+    GT_CUDA(cudaMemcpyAsync(fs->d_rows[k].p, rows.data(), sizeof(uint32_t) * n, cudaMemcpyHostToDevice, e->stream));
+    h_row_ptrs[k] = fs->d_rows[k].p;
+    h_ntrain[k] = fs->ntrain[k];
+    size_t ntr = (size_t)fs->ntrain[k];
+    size_t n_bins = std::max<size_t>(1, std::min<size_t>(ntr, GT_MAX_BIN));
+    double eps = 1.0 / (double)((float)n_bins * 8.0f);
+    size_t nl, lim;
+    limit_size_level(std::max<size_t>(ntr, 1), eps, &nl, &lim);
+    h_limit[k] = (int)lim;
+    lmax = std::max(lmax, lim); nlevel_max = std::max(nlevel_max, nl);
+    for (int64_t q = 0; q < fs->ntrain[k]; ++q) {
+      float y = e->h_y[rows[q]];
+      if (y == 1.0f) fs->n1[k]++;
+      else { fs->nnot1[k]++; fs->sum_not1_sq[k] += (double)(0.0f - y); fs->sum_not1_lg[k] += (double)(0.5f - y); }
+    }
+  }
+  // ---- sketch -> cuts
+  GT_CUDA(fs->d_cuts.ensure((size_t)nfold * f * GT_MAX_BIN));
+  GT_CUDA(fs->d_ncuts.ensure((size_t)nfold * f));
+  GT_CUDA(cudaMemsetAsync(fs->d_cuts.p, 0, sizeof(float) * (size_t)nfold * f * GT_MAX_BIN, e->stream));
+  {
+    gt::SketchPlan plan;
+    plan.buf_cap = (int)(2 * lmax + 2);
+    plan.nlevel_alloc = (int)nlevel_max + 3;
+    int kp = 2; while (kp < (int)(2 * lmax)) kp <<= 1;
+    plan.keys_per_stream = kp;
+    plan.entries_per_stream = 3ll * plan.buf_cap + (long long)plan.nlevel_alloc * (long long)lmax;
+    const int streams = nfold * f;
+    size_t per_stream = (size_t)plan.keys_per_stream * 8 + (size_t)plan.entries_per_stream * 16;
+    size_t free_b = 0, total_b = 0;
+    GT_CUDA(cudaMemGetInfo(&free_b, &total_b));
+    size_t room = (size_t)(0.6 * (double)free_b);
+    int per_launch = (int)std::max<size_t>(1, std::min<size_t>((size_t)streams, room / std::max<size_t>(per_stream, 1)));
+    DevBuf<unsigned long long> keys;
+    DevBuf<float4> ents;
+    DevBuf<const uint32_t*> d_row_ptrs;
+    DevBuf<long long> d_ntrain;
+    DevBuf<int> d_limit;
+    GT_CUDA(keys.ensure((size_t)per_launch * plan.keys_per_stream));
+    GT_CUDA(ents.ensure((size_t)per_launch * (size_t)plan.entries_per_stream));
+    GT_CUDA(d_row_ptrs.ensure(nfold)); GT_CUDA(d_ntrain.ensure(nfold)); GT_CUDA(d_limit.ensure(nfold));
+    GT_CUDA(cudaMemcpyAsync(d_row_ptrs.p, h_row_ptrs.data(), sizeof(void*) * nfold, cudaMemcpyHostToDevice, e->stream));
+    GT_CUDA(cudaMemcpyAsync(d_ntrain.p, h_ntrain.data(), sizeof(long long) * nfold, cudaMemcpyHostToDevice, e->stream));
+    GT_CUDA(cudaMemcpyAsync(d_limit.p, h_limit.data(), sizeof(int) * nfold, cudaMemcpyHostToDevice, e->stream));
+    for (int s0 = 0; s0 < streams; s0 += per_launch) {
+      int cnt = std::min(per_launch, streams - s0);
+      gt::launch_sketch(e->d_X, e->ldx, f, nfold, d_row_ptrs.p, d_ntrain.p, plan, d_limit.p, keys.p, ents.p,
+                        fs->d_cuts.p, fs->d_ncuts.p, s0, cnt, e->stream);
+      GT_CUDA(cudaGetLastError());
+    }
+    GT_CUDA(cudaStreamSynchronize(e->stream));   // arenas are released on scope exit
+  }
+  // ---- bins + labels in fold order
+  std::vector<gt::FoldDev> h_folds(nfold);
+  for (int k = 0; k < nfold; ++k) {
+    GT_CUDA(fs->d_bins[k].ensure((size_t)n * e->fpad));
+    GT_CUDA(fs->d_y[k].ensure(n));
+    gt::launch_bin(e->d_X, e->ldx, f, e->fpad, fs->d_rows[k].p, n, fs->d_cuts.p + (size_t)k * f * GT_MAX_BIN,
+                   fs->d_ncuts.p + (size_t)k * f, fs->d_bins[k].p, e->stream);
+    GT_CUDA(cudaGetLastError());
+    gt::launch_gather_y(e->d_y, fs->d_rows[k].p, n, fs->d_y[k].p, e->stream);
+    GT_CUDA(cudaGetLastError());
+    h_folds[k].bins = fs->d_bins[k].p; h_folds[k].y = fs->d_y[k].p;
+    h_folds[k].cuts = fs->d_cuts.p + (size_t)k * f * GT_MAX_BIN; h_folds[k].ncuts = fs->d_ncuts.p + (size_t)k * f;
+    h_folds[k].ntrain = fs->ntrain[k]; h_folds[k].ntest = fs->ntest[k];
+  }
+  fs->h_ncuts.resize((size_t)nfold * f);
+  GT_CUDA(cudaMemcpyAsync(fs->h_ncuts.data(), fs->d_ncuts.p, sizeof(int) * (size_t)nfold * f, cudaMemcpyDeviceToHost, e->stream));
+  GT_CUDA(cudaStreamSynchronize(e->stream));
+  std::vector<int> h_maxnc((size_t)nfold * e->groups, 0);
+  for (int k = 0; k < nfold; ++k)
+    for (int j = 0; j < f; ++j) {
+      int& m = h_maxnc[(size_t)k * e->groups + j / gt::kLanes];
+      m = std::max(m, fs->h_ncuts[(size_t)k * f + j]);
+    }
+  GT_CUDA(fs->d_grp_maxnc.ensure(h_maxnc.size()));
+  GT_CUDA(cudaMemcpyAsync(fs->d_grp_maxnc.p, h_maxnc.data(), sizeof(int) * h_maxnc.size(), cudaMemcpyHostToDevice, e->stream));
+  GT_CUDA(fs->d_folds.ensure(nfold));
+  GT_CUDA(cudaMemcpyAsync(fs->d_folds.p, h_folds.data(), sizeof(gt::FoldDev) * nfold, cudaMemcpyHostToDevice, e->stream));
+  GT_CUDA(cudaEventRecord(ev1, e->stream));
+  GT_CUDA(cudaStreamSynchronize(e->stream));
+  float ms = 0;
+  GT_CUDA(cudaEventElapsedTime(&ms, ev0, ev1));
+  cudaEventDestroy(ev0); cudaEventDestroy(ev1);
+  fs->prepare_ms = ms;
+  e->stats.prepare_ms = ms;
+  *out = fs.get();
+  e->foldsets[nfold] = std::move(fs);
+  return GT_OK;
+}
+
+struct Genes { double v[GT_NUM_GENES]; };
+
+float base_margin_for(const FoldSet& fs, int k, int objective, float spw) {
+  // FitIntercept::InitEstimation: gradient at margin 0, one Newton step, PredTransform, ProbToMargin
+  double sg, sh;
+  if (objective == GT_OBJ_LOGISTIC) {
+    float g1 = (0.5f - 1.0f) * spw, h1 = 0.25f * spw;
+    sg = fs.sum_not1_lg[k] + (double)fs.n1[k] * (double)g1;
+    sh = (double)fs.nnot1[k] * 0.25 + (double)fs.n1[k] * (double)h1;
+  } else {
+    float g1 = (0.0f - 1.0f) * spw, h1 = 1.0f * spw;
+    sg = fs.sum_not1_sq[k] + (double)fs.n1[k] * (double)g1;
+    sh = (double)fs.nnot1[k] + (double)fs.n1[k] * (double)h1;
+  }
+  float stump = (float)(-sg / std::max(sh, 1e-6));
+  if (objective == GT_OBJ_LOGISTIC) {
+    float x = std::fmin(-stump, 88.7f);
+    float bs = 1.0f / (std::exp(x) + 1.0f + 1e-16f);
+    return -std::log(1.0f / bs - 1.0f);
+  }
+  return stump;
+}
+
+size_t hist_cells_for_depth(int D, int groups) {
+  // ping-pong level buffers: the largest even level and the largest odd level that get histograms
+  int last = D - 1;                      // deepest level with histograms
+  int even = last - (last & 1), odd = last - 1 + (last & 1);
+  size_t cells = (size_t)1 << even;
+  if (odd >= 1) cells += (size_t)1 << odd;
+  return cells * (size_t)groups * gt::kBins * gt::kLanes;
+}
+
+int eval_impl(gt_engine* e, int n_ind, const double* genes, const gt_fit_opts* o, double* fitness_out,
+              int32_t* rounds_out, const gt_dump* dump) {
+  if (!e || !genes || !o || !fitness_out || n_ind < 0) return fail(GT_ERR_ARG, "null argument");
+  if (o->objective != GT_OBJ_SQUAREDERROR && o->objective != GT_OBJ_LOGISTIC) return fail(GT_ERR_ARG, "unknown objective %d", o->objective);
+  if (o->metric != GT_METRIC_RMSE && o->metric != GT_METRIC_LOGLOSS) return fail(GT_ERR_ARG, "unknown metric %d", o->metric);
+  if (o->num_boost_round < 1) return fail(GT_ERR_ARG, "num_boost_round must be >= 1");
+  for (int i = 0; i < n_ind; ++i) {
+    const double* g = genes + (size_t)i * GT_NUM_GENES;
+    for (int q = 0; q < GT_NUM_GENES; ++q) if (!std::isfinite(g[q])) return fail(GT_ERR_ARG, "individual %d: gene %d is not finite", i, q);
+    if (g[2] != std::floor(g[2]) || g[2] < 1 || g[2] > gt::kMaxDepth) return fail(GT_ERR_ARG, "individual %d: max_depth=%g outside 1..%d", i, g[2], gt::kMaxDepth);
+    if (g[0] < 0) return fail(GT_ERR_ARG, "individual %d: eta < 0", i);
+    if (g[1] < 0 || g[3] < 0 || g[4] < 0 || g[8] < 0 || g[9] < 0) return fail(GT_ERR_ARG, "individual %d: negative regulariser", i);
+    for (int q = 5; q <= 7; ++q) if (g[q] < 0 || g[q] > 1) return fail(GT_ERR_ARG, "individual %d: sampling gene %d=%g outside [0,1]", i, q, g[q]);
+    if (g[10] < 0) return fail(GT_ERR_ARG, "individual %d: scale_pos_weight < 0", i);
+  }
+  if (n_ind == 0) return GT_OK;
+  GT_CUDA(cudaSetDevice(e->device));
+  FoldSet* fs = nullptr;
+  int rc = prepare_impl(e, o->nfold, &fs);
+  if (rc != GT_OK) return rc;
+  const int nfold = o->nfold;
+  const int64_t n = e->n;
+  int64_t ntmax = 0;
+  for (int k = 0; k < nfold; ++k) ntmax = std::max(ntmax, fs->ntrain[k]);
+  const int64_t nt_stride = (ntmax + 31) / 32 * 32;
+  const int hist_cap = (int)(nt_stride / gt::kHistRows + 514);
+  const int part_cap = (int)(nt_stride / gt::kPartRows + 514);
+  const int pair_cap = 512;
+  const int pred_chunks = (int)((n + gt::kPredRows - 1) / gt::kPredRows);
+
+  // order by depth so that a wave's level loop is not held open by one deep individual
+  std::vector<int> order(n_ind);
+  for (int i = 0; i < n_ind; ++i) order[i] = i;
+  std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return genes[(size_t)a * GT_NUM_GENES + 2] > genes[(size_t)b * GT_NUM_GENES + 2]; });
+
+  auto job_bytes = [&](int D) -> size_t {
+    size_t b = (size_t)n * 4 + (size_t)nt_stride * 8 + (size_t)nt_stride * 8;
+    b += hist_cells_for_depth(D, e->groups) * sizeof(gt::HistEntry);
+    b += (size_t)gt::kNodeCap * (sizeof(gt::Node) + sizeof(gt::TreeNode));
+    b += (size_t)hist_cap * (sizeof(gt::HistItem) + 4) + (size_t)pair_cap * sizeof(gt::PairRec);
+    b += (size_t)part_cap * (sizeof(gt::PartItem) + gt::kPartRows / 8 + 4) + (size_t)pred_chunks * 8;
+    b += sizeof(gt::JobParams) + sizeof(gt::JobState);
+    return b;
+  };
+  size_t free_b = 0, total_b = 0;
+  GT_CUDA(cudaMemGetInfo(&free_b, &total_b));
+  size_t budget = e->mem_budget > 0 ? (size_t)e->mem_budget : (size_t)(0.85 * (double)free_b);
+  std::vector<std::pair<int, int>> waves;   // [begin, end) in `order`
+  {
+    int b = 0;
+    while (b < n_ind) {
+      size_t used = 0; int q = b;
+      while (q < n_ind && (q - b + 1) * nfold <= 16384) {
+        size_t need = job_bytes((int)genes[(size_t)order[q] * GT_NUM_GENES + 2]) * (size_t)nfold;
+        if (used + need > budget) break;
+        used += need; ++q;
+      }
+      if (q == b) return fail(GT_ERR_NOMEM, "device memory budget %zu B cannot hold one individual (%zu B)", budget,
+                              job_bytes((int)genes[(size_t)order[b] * GT_NUM_GENES + 2]) * (size_t)nfold);
+      waves.emplace_back(b, q);
+      b = q;
+    }
+  }
+  size_t max_jobs = 0, max_inds = 0, max_hist = 0;
+  for (auto& wv : waves) {
+    size_t inds = wv.second - wv.first, hc = 0;
+    for (int q = wv.first; q < wv.second; ++q) hc += hist_cells_for_depth((int)genes[(size_t)order[q] * GT_NUM_GENES + 2], e->groups) * nfold;
+    max_inds = std::max(max_inds, inds); max_jobs = std::max(max_jobs, inds * nfold); max_hist = std::max(max_hist, hc);
+  }
+  DevBuf<gt::JobParams> d_jp; DevBuf<gt::JobState> d_js; DevBuf<gt::IndState> d_is;
+  DevBuf<gt::Node> d_nodes; DevBuf<gt::TreeNode> d_tree; DevBuf<float> d_pred; DevBuf<int2> d_gq;
+  DevBuf<uint32_t> d_ridx; DevBuf<gt::HistEntry> d_hist; DevBuf<gt::HistItem> d_hitems; DevBuf<int> d_zlist;
+  DevBuf<gt::PairRec> d_pairs; DevBuf<gt::PartItem> d_pitems; DevBuf<uint32_t> d_pbits; DevBuf<int> d_pleft;
+  DevBuf<double> d_mpart; DevBuf<double> d_trace; DevBuf<unsigned long long> d_counters;
+  DevBuf<double> d_fit; DevBuf<int> d_rounds; DevBuf<gt_tree_node> d_trees; DevBuf<gt_node_rows> d_nrows;
+  GT_CUDA(d_jp.ensure(max_jobs)); GT_CUDA(d_js.ensure(max_jobs)); GT_CUDA(d_is.ensure(max_inds));
+  GT_CUDA(d_nodes.ensure(max_jobs * gt::kNodeCap)); GT_CUDA(d_tree.ensure(max_jobs * gt::kNodeCap));
+  GT_CUDA(d_pred.ensure(max_jobs * (size_t)n)); GT_CUDA(d_gq.ensure(max_jobs * (size_t)nt_stride));
+  GT_CUDA(d_ridx.ensure(max_jobs * 2 * (size_t)nt_stride)); GT_CUDA(d_hist.ensure(max_hist));
+  GT_CUDA(d_hitems.ensure(max_jobs * hist_cap)); GT_CUDA(d_zlist.ensure(max_jobs * hist_cap));
+  GT_CUDA(d_pairs.ensure(max_jobs * pair_cap)); GT_CUDA(d_pitems.ensure(max_jobs * part_cap));
+  GT_CUDA(d_pbits.ensure(max_jobs * (size_t)part_cap * (gt::kPartRows / 32))); GT_CUDA(d_pleft.ensure(max_jobs * part_cap));
+  GT_CUDA(d_mpart.ensure(max_jobs * pred_chunks)); GT_CUDA(d_counters.ensure(8));
+  GT_CUDA(d_fit.ensure(n_ind)); GT_CUDA(d_rounds.ensure(n_ind));
+  const bool want_trace = dump && dump->trace_means;
+  const int tree_rounds = (dump && dump->trees) ? std::min(dump->tree_rounds, o->num_boost_round) : 0;
+  const bool want_rows = dump && dump->row_sets && dump->node_rows && dump->rows_round >= 0;
+  if (want_trace) GT_CUDA(d_trace.ensure(max_inds * (size_t)o->num_boost_round));
+  if (tree_rounds) GT_CUDA(d_trees.ensure(max_jobs * (size_t)tree_rounds * GT_MAX_NODES));
+  if (want_rows) GT_CUDA(d_nrows.ensure(max_jobs * (size_t)GT_MAX_NODES));
+  if (want_rows && dump->row_stride < nt_stride) return fail(GT_ERR_ARG, "row_stride %lld < %lld", (long long)dump->row_stride, (long long)nt_stride);
+  GT_CUDA(cudaMemsetAsync(d_counters.p, 0, 8 * sizeof(unsigned long long), e->stream));
+  GT_CUDA(cudaMemsetAsync(d_fit.p, 0xff, sizeof(double) * n_ind, e->stream));   // NaN until written
+  GT_CUDA(cudaMemsetAsync(d_rounds.p, 0, sizeof(int) * n_ind, e->stream));
+
+  rc = gt::configure_kernels();
+  if (rc != 0) return fail(GT_ERR_CUDA, "cudaFuncSetAttribute failed: %s", cudaGetErrorString((cudaError_t)rc));
+
+  std::vector<cudaEvent_t> ev;   // hist timing pairs
+  auto get_event = [&](size_t idx) -> cudaEvent_t {
+    while (ev.size() <= idx) { cudaEvent_t x; cudaEventCreate(&x); ev.push_back(x); }
+    return ev[idx];
+  };
+  size_t ev_used = 0;
+  double hist_ms = 0;
+  long long launches = 0, hist_launches = 0;
+  cudaEvent_t e0, e1;
+  GT_CUDA(cudaEventCreate(&e0)); GT_CUDA(cudaEventCreate(&e1));
+  GT_CUDA(cudaEventRecord(e0, e->stream));
+  auto drain_events = [&]() {
+    for (size_t q = 0; q + 1 < ev_used; q += 2) { float ms = 0; cudaEventElapsedTime(&ms, ev[q], ev[q + 1]); hist_ms += ms; }
+    ev_used = 0;
+  };
+
+  for (auto& wv : waves) {
+    const int inds = wv.second - wv.first, jobs = inds * nfold;
+    std::vector<gt::JobParams> h_jp(jobs);
+    std::vector<gt::JobState> h_js(jobs);
+    std::vector<gt::IndState> h_is(inds);
+    size_t hoff = 0;
+    int Dmax = 1;
+    for (int q = 0; q < inds; ++q) {
+      const int src = order[wv.first + q];
+      const double* g = genes + (size_t)src * GT_NUM_GENES;
+      gt::IndState& is = h_is[q];
+      memset(&is, 0, sizeof(is));
+      is.active = 1; is.out_index = src;
+      const int D = (int)g[2];
+      Dmax = std::max(Dmax, D);
+      for (int k = 0; k < nfold; ++k) {
+        gt::JobParams& p = h_jp[q * nfold + k];
+        memset(&p, 0, sizeof(p));
+        p.eta = (float)g[0]; p.mcw = (float)g[1]; p.max_depth = D; p.gamma = (float)g[3]; p.mds = (float)g[4];
+        p.subsample = (float)g[5]; p.coltree = (float)g[6]; p.collevel = (float)g[7]; p.lambda = (float)g[8];
+        p.alpha = (float)g[9]; p.spw = (float)g[10];
+        p.fold = k; p.ind = q;
+        p.base_margin = base_margin_for(*fs, k, o->objective, p.spw);
+        const int last = D - 1;
+        const int even = last - (last & 1), odd = last - 1 + (last & 1);
+        p.hist_off[0] = hoff; hoff += ((size_t)1 << even) * e->groups * gt::kBins * gt::kLanes;
+        p.hist_off[1] = hoff; if (odd >= 1) hoff += ((size_t)1 << odd) * e->groups * gt::kBins * gt::kLanes;
+        gt::JobState& s = h_js[q * nfold + k];
+        memset(&s, 0, sizeof(s));
+        s.active = 1;
+      }
+    }
+    GT_CUDA(cudaMemcpyAsync(d_jp.p, h_jp.data(), sizeof(gt::JobParams) * jobs, cudaMemcpyHostToDevice, e->stream));
+    GT_CUDA(cudaMemcpyAsync(d_js.p, h_js.data(), sizeof(gt::JobState) * jobs, cudaMemcpyHostToDevice, e->stream));
+    GT_CUDA(cudaMemcpyAsync(d_is.p, h_is.data(), sizeof(gt::IndState) * inds, cudaMemcpyHostToDevice, e->stream));
+    GT_CUDA(cudaMemsetAsync(d_nodes.p, 0, sizeof(gt::Node) * (size_t)jobs * gt::kNodeCap, e->stream));
+    GT_CUDA(cudaMemsetAsync(d_tree.p, 0, sizeof(gt::TreeNode) * (size_t)jobs * gt::kNodeCap, e->stream));
+    unsigned long long act = (unsigned long long)inds;
+    GT_CUDA(cudaMemcpyAsync(d_counters.p + 2, &act, sizeof(act), cudaMemcpyHostToDevice, e->stream));
+    if (want_trace) GT_CUDA(cudaMemsetAsync(d_trace.p, 0xff, sizeof(double) * (size_t)inds * o->num_boost_round, e->stream));
+
+    gt::Wave w;
+    memset(&w, 0, sizeof(w));
+    w.n_jobs = jobs; w.n_inds = inds; w.nfold = nfold; w.n = n; w.nt_stride = nt_stride;
+    w.f = e->f; w.fpad = e->fpad; w.groups = e->groups;
+    w.objective = o->objective; w.metric = o->metric; w.num_boost_round = o->num_boost_round;
+    w.early_stopping_rounds = o->early_stopping_rounds;
+    w.hist_cap = hist_cap; w.pair_cap = pair_cap; w.part_cap = part_cap; w.pred_chunks = pred_chunks;
+    w.folds = fs->d_folds.p; w.grp_maxnc = fs->d_grp_maxnc.p;
+    w.jp = d_jp.p; w.js = d_js.p; w.is = d_is.p; w.nodes = d_nodes.p; w.tree = d_tree.p; w.pred = d_pred.p;
+    w.gq = d_gq.p; w.ridx = d_ridx.p; w.hist = d_hist.p; w.hitems = d_hitems.p; w.zlist = d_zlist.p;
+    w.pairs = d_pairs.p; w.pitems = d_pitems.p; w.pbits = d_pbits.p; w.pleft = d_pleft.p; w.mpart = d_mpart.p;
+    w.trace = want_trace ? d_trace.p : nullptr; w.counters = d_counters.p;
+
+    gt::launch_init_wave(w, e->stream); ++launches;
+    gt::launch_round_end(w, 1, d_fit.p, d_rounds.p, e->stream); ++launches;
+    GT_CUDA(cudaGetLastError());
+    const bool can_stop_early = o->early_stopping_rounds > 0 && o->early_stopping_rounds < o->num_boost_round;
+    for (int round = 0; round < o->num_boost_round; ++round) {
+      gt::launch_grad(w, e->stream); ++launches;
+      for (int d = 0; d < Dmax; ++d) {
+        gt::launch_plan_hist(w, d, e->stream);
+        gt::launch_hist_zero(w, d, e->stream);
+        if (e->collect_timing) cudaEventRecord(get_event(ev_used++), e->stream);
+        gt::launch_hist(w, d, e->stream);
+        if (e->collect_timing) cudaEventRecord(get_event(ev_used++), e->stream);
+        gt::launch_scan(w, d, e->stream);
+        launches += 4; ++hist_launches;
+        if (d + 1 < Dmax) {
+          gt::launch_plan_part(w, d, e->stream);
+          gt::launch_part_count(w, d, e->stream);
+          gt::launch_part_scatter(w, d, e->stream);
+          launches += 3;
+        }
+      }
+      if (round < tree_rounds) { gt::launch_dump_trees(w, round, tree_rounds, d_trees.p, e->stream); ++launches; }
+      if (want_rows && round == dump->rows_round) {
+        gt::launch_dump_node_rows(w, d_nrows.p, e->stream); ++launches;
+        GT_CUDA(cudaStreamSynchronize(e->stream));
+        for (int q = 0; q < inds; ++q)
+          for (int k = 0; k < nfold; ++k) {
+            const size_t dst = ((size_t)h_is[q].out_index * nfold + k);
+            const int j = q * nfold + k;
+            for (int b = 0; b < 2; ++b)
+              GT_CUDA(cudaMemcpy(dump->row_sets + (dst * 2 + b) * (size_t)dump->row_stride, d_ridx.p + ((size_t)j * 2 + b) * nt_stride,
+                                 sizeof(uint32_t) * (size_t)nt_stride, cudaMemcpyDeviceToHost));
+            GT_CUDA(cudaMemcpy(dump->node_rows + dst * GT_MAX_NODES, d_nrows.p + (size_t)j * GT_MAX_NODES,
+                               sizeof(gt_node_rows) * GT_MAX_NODES, cudaMemcpyDeviceToHost));
+          }
+      }
+      gt::launch_predict(w, e->stream);
+      gt::launch_round_end(w, 0, d_fit.p, d_rounds.p, e->stream);
+      launches += 2;
+      if (e->collect_timing && ev_used >= 4096) { GT_CUDA(cudaStreamSynchronize(e->stream)); drain_events(); }
+      if (can_stop_early && (round % 8 == 7)) {
+        unsigned long long left = 0;
+        GT_CUDA(cudaMemcpyAsync(&left, d_counters.p + 2, sizeof(left), cudaMemcpyDeviceToHost, e->stream));
+        GT_CUDA(cudaStreamSynchronize(e->stream));
+        if (left == 0) break;
+      }
+    }
+    GT_CUDA(cudaStreamSynchronize(e->stream));
+    GT_CUDA(cudaGetLastError());
+    if (e->collect_timing) drain_events();
+    if (want_trace) {
+      std::vector<double> h((size_t)inds * o->num_boost_round);
+      GT_CUDA(cudaMemcpy(h.data(), d_trace.p, sizeof(double) * h.size(), cudaMemcpyDeviceToHost));
+      for (int q = 0; q < inds; ++q)
+        memcpy(dump->trace_means + (size_t)h_is[q].out_index * o->num_boost_round, h.data() + (size_t)q * o->num_boost_round,
+               sizeof(double) * o->num_boost_round);
+    }
+    if (tree_rounds) {
+      for (int q = 0; q < inds; ++q)
+        for (int k = 0; k < nfold; ++k)
+          GT_CUDA(cudaMemcpy(dump->trees + (((size_t)h_is[q].out_index * nfold + k) * dump->tree_rounds) * GT_MAX_NODES,
+                             d_trees.p + ((size_t)(q * nfold + k) * tree_rounds) * GT_MAX_NODES,
+                             sizeof(gt_tree_node) * (size_t)tree_rounds * GT_MAX_NODES, cudaMemcpyDeviceToHost));
+    }
+  }
+  GT_CUDA(cudaEventRecord(e1, e->stream));
+  GT_CUDA(cudaMemcpyAsync(fitness_out, d_fit.p, sizeof(double) * n_ind, cudaMemcpyDeviceToHost, e->stream));
+  std::vector<int> h_rounds(n_ind);
+  GT_CUDA(cudaMemcpyAsync(h_rounds.data(), d_rounds.p, sizeof(int) * n_ind, cudaMemcpyDeviceToHost, e->stream));
+  unsigned long long h_counters[8];
+  GT_CUDA(cudaMemcpyAsync(h_counters, d_counters.p, sizeof(h_counters), cudaMemcpyDeviceToHost, e->stream));
+  GT_CUDA(cudaStreamSynchronize(e->stream));
+  if (rounds_out) for (int i = 0; i < n_ind; ++i) rounds_out[i] = h_rounds[i];
+  float ms = 0;
+  GT_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  for (auto x : ev) cudaEventDestroy(x);
+  e->stats.eval_ms = ms;
+  e->stats.hist_ms = hist_ms;
+  e->stats.hist_launches = hist_launches;
+  e->stats.kernel_launches = launches;
+  e->stats.waves = (int64_t)waves.size();
+  e->stats.jobs = (int64_t)n_ind * nfold;
+  // algorithmic bytes of the histogram launches: rows x (F bin bytes + 8 B (g,h) + 4 B row id)
+  // + one F x 256 x 16 B histogram written per built node
+  e->stats.hist_row_features = (double)h_counters[0] * (double)e->f;
+  e->stats.hist_alg_bytes = (double)h_counters[0] * ((double)e->f + 12.0) + (double)h_counters[1] * (double)e->f * 256.0 * 16.0;
+  for (int i = 0; i < n_ind; ++i)
+    if (!std::isfinite(fitness_out[i])) return fail(GT_ERR_STATE, "individual %d produced a non-finite fitness", i);
+  return GT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int gt_engine_create(const float* X, int64_t n, int32_t f, int64_t ldx, const float* y, const gt_data_opts* opts,
+                     gt_engine** out) {
+  if (!X || !y || !out || n < 2 || f < 1 || ldx < f) return fail(GT_ERR_ARG, "bad data arguments");
+  if (f > 256) return fail(GT_ERR_ARG, "f=%d exceeds 256 features", f);
+  if (n >= (1ll << 31)) return fail(GT_ERR_ARG, "n=%lld exceeds 2^31 rows", (long long)n);
+  int count = 0;
+  cudaError_t ce = cudaGetDeviceCount(&count);
+  if (ce != cudaSuccess || count == 0)
+    return fail(GT_ERR_CUDA, "no CUDA device available (%s); this engine has no CPU path", cudaGetErrorString(ce));
+  std::unique_ptr<gt_engine> e(new gt_engine());
+  e->device = opts ? opts->device : 0;
+  if (e->device < 0 || e->device >= count) return fail(GT_ERR_ARG, "device %d out of range (%d devices)", e->device, count);
+  e->mem_budget = opts ? opts->mem_budget_bytes : 0;
+  e->collect_timing = opts ? opts->reserved[0] : 0;
+  e->n = n; e->f = f; e->ldx = ldx;
+  e->fpad = (f + gt::kLanes - 1) / gt::kLanes * gt::kLanes;
+  e->groups = e->fpad / gt::kLanes;
+  GT_CUDA(cudaSetDevice(e->device));
+  GT_CUDA(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+  e->h_y.resize(n);
+  if (opts && opts->x_on_device) {
+    e->d_X = X; e->d_y = y;
+    GT_CUDA(cudaMemcpy(e->h_y.data(), y, sizeof(float) * n, cudaMemcpyDeviceToHost));
+  } else {
+    GT_CUDA(e->own_X.ensure((size_t)n * ldx));
+    GT_CUDA(e->own_y.ensure(n));
+    GT_CUDA(cudaMemcpyAsync(e->own_X.p, X, sizeof(float) * (size_t)n * ldx, cudaMemcpyHostToDevice, e->stream));
+    GT_CUDA(cudaMemcpyAsync(e->own_y.p, y, sizeof(float) * n, cudaMemcpyHostToDevice, e->stream));
+    GT_CUDA(cudaStreamSynchronize(e->stream));
+    memcpy(e->h_y.data(), y, sizeof(float) * n);
+    e->d_X = e->own_X.p; e->d_y = e->own_y.p;
+  }
+  *out = e.release();
+  return GT_OK;
+}
+
+int gt_engine_prepare(gt_engine* e, int32_t nfold) {
+  if (!e) return fail(GT_ERR_ARG, "null engine");
+  FoldSet* fs = nullptr;
+  return prepare_impl(e, nfold, &fs);
+}
+
+int gt_engine_eval(gt_engine* e, int32_t n_ind, const double* genes, const gt_fit_opts* opts, double* fitness_out,
+                   int32_t* rounds_out) {
+  return eval_impl(e, n_ind, genes, opts, fitness_out, rounds_out, nullptr);
+}
+
+int gt_engine_eval_ex(gt_engine* e, int32_t n_ind, const double* genes, const gt_fit_opts* opts, double* fitness_out,
+                      int32_t* rounds_out, const gt_dump* dump) {
+  return eval_impl(e, n_ind, genes, opts, fitness_out, rounds_out, dump);
+}
+
+void gt_engine_destroy(gt_engine* e) {
+  if (!e) return;
+  cudaSetDevice(e->device);
+  if (e->stream) { cudaStreamSynchronize(e->stream); }
+  e->foldsets.clear();
+  if (e->stream) cudaStreamDestroy(e->stream);
+  delete e;
+}
+
+int gt_engine_fold_sizes(gt_engine* e, int32_t nfold, int32_t k, int64_t* ntrain, int64_t* ntest) {
+  if (!e) return fail(GT_ERR_ARG, "null engine");
+  FoldSet* fs = nullptr;
+  int rc = prepare_impl(e, nfold, &fs);
+  if (rc != GT_OK) return rc;
+  if (k < 0 || k >= nfold) return fail(GT_ERR_ARG, "fold %d out of range", k);
+  if (ntrain) *ntrain = fs->ntrain[k];
+  if (ntest) *ntest = fs->ntest[k];
+  return GT_OK;
+}
+
+int gt_engine_get_fold_rows(gt_engine* e, int32_t nfold, int32_t k, int64_t* train_rows, int64_t* test_rows) {
+  if (!e) return fail(GT_ERR_ARG, "null engine");
+  FoldSet* fs = nullptr;
+  int rc = prepare_impl(e, nfold, &fs);
+  if (rc != GT_OK) return rc;
+  if (k < 0 || k >= nfold) return fail(GT_ERR_ARG, "fold %d out of range", k);
+  // read the device copy back so the test sees what the kernels see
+  std::vector<uint32_t> h(e->n);
+  GT_CUDA(cudaMemcpy(h.data(), fs->d_rows[k].p, sizeof(uint32_t) * e->n, cudaMemcpyDeviceToHost));
+  if (train_rows) for (int64_t i = 0; i < fs->ntrain[k]; ++i) train_rows[i] = h[i];
+  if (test_rows) for (int64_t i = 0; i < fs->ntest[k]; ++i) test_rows[i] = h[fs->ntrain[k] + i];
+  return GT_OK;
+}
+
+int gt_engine_get_cuts(gt_engine* e, int32_t nfold, int32_t k, float* cuts, int32_t* ncuts) {
+  if (!e) return fail(GT_ERR_ARG, "null engine");
+  FoldSet* fs = nullptr;
+  int rc = prepare_impl(e, nfold, &fs);
+  if (rc != GT_OK) return rc;
+  if (k < 0 || k >= nfold) return fail(GT_ERR_ARG, "fold %d out of range", k);
+  if (cuts) GT_CUDA(cudaMemcpy(cuts, fs->d_cuts.p + (size_t)k * e->f * GT_MAX_BIN, sizeof(float) * (size_t)e->f * GT_MAX_BIN, cudaMemcpyDeviceToHost));
+  if (ncuts) GT_CUDA(cudaMemcpy(ncuts, fs->d_ncuts.p + (size_t)k * e->f, sizeof(int) * e->f, cudaMemcpyDeviceToHost));
+  return GT_OK;
+}
+
+int gt_engine_get_bins(gt_engine* e, int32_t nfold, int32_t k, uint8_t* bins) {
+  if (!e || !bins) return fail(GT_ERR_ARG, "null argument");
+  FoldSet* fs = nullptr;
+  int rc = prepare_impl(e, nfold, &fs);
+  if (rc != GT_OK) return rc;
+  if (k < 0 || k >= nfold) return fail(GT_ERR_ARG, "fold %d out of range", k);
+  GT_CUDA(cudaMemcpy2D(bins, e->f, fs->d_bins[k].p, e->fpad, e->f, e->n, cudaMemcpyDeviceToHost));
+  return GT_OK;
+}
+
+int gt_engine_get_stats(gt_engine* e, gt_stats* out) {
+  if (!e || !out) return fail(GT_ERR_ARG, "null argument");
+  *out = e->stats;
+  return GT_OK;
+}
+
+int gt_make_folds(int64_t n, int32_t nfold, uint32_t seed, int64_t* perm, int64_t* fold_begin) {
+  if (n < 1 || nfold < 1 || !perm || !fold_begin) return fail(GT_ERR_ARG, "bad arguments");
+  make_folds_host(n, nfold, seed, perm, fold_begin);
+  return GT_OK;
+}
+
+const char* gt_last_error(void) { return g_err.c_str(); }
+int gt_version(void) { return 100; }
+
+}  // extern "C"

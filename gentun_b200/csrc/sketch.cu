@@ -1,0 +1,362 @@
+// X2/X3 of the hot path: per-fold weighted quantile sketch -> cut points, and value -> uint8 bin.
+//
+// Replaces what every xgboost Booster does lazily inside xgb.cv (call site
+// /root/reference/gentun/models/xgboost_models.py:33-36): HostSketchContainer / WQuantileSketch
+// (upstream src/common/quantile.{h,cc}) over the rows of each fold's train slice in slice order,
+// then GHistIndexMatrix binning (upstream src/common/hist_util.h SearchBin).  The sketch is an
+// order-dependent streaming algorithm; it is reproduced stream by stream (one CTA per
+// fold x feature), with the queue fill expressed as a run-length scan and the queue sort as a
+// CTA-wide bitonic network, and the summary merge/prune hierarchy walked by one thread.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace gt {
+
+namespace {
+
+constexpr int kSketchThreads = 1024;
+
+struct Summary { float4* d; int size; };   // float4 = (rmin, rmax, wmin, value)
+
+__device__ __forceinline__ float rmin_next(const float4& e) { return __fadd_rn(e.x, e.z); }
+__device__ __forceinline__ float rmax_prev(const float4& e) { return __fsub_rn(e.y, e.z); }
+
+__device__ void s_copy(Summary& dst, const Summary& src) {
+  for (int i = 0; i < src.size; ++i) dst.d[i] = src.d[i];
+  dst.size = src.size;
+}
+
+// WQSummary::SetPrune
+__device__ void s_prune(Summary& dst, const Summary& src, int maxsize) {
+  if (src.size <= maxsize) { s_copy(dst, src); return; }
+  const float begin = src.d[0].y;
+  const float range = __fsub_rn(src.d[src.size - 1].x, src.d[0].y);
+  const int n = maxsize - 1;
+  const float fn = (float)n;
+  dst.d[0] = src.d[0];
+  int out = 1;
+  int i = 1, lastidx = 0;
+  float4 cur = src.d[1];       // src[i]
+  float4 nxt = src.d[i + 1 < src.size ? i + 1 : i];   // src[i+1]
+  for (int k = 1; k < n; ++k) {
+    float dx2 = __fmul_rn(2.0f, __fadd_rn(__fdiv_rn(__fmul_rn((float)k, range), fn), begin));
+    while (i < src.size - 1 && dx2 >= __fadd_rn(nxt.y, nxt.x)) {
+      ++i; cur = nxt;
+      if (i + 1 < src.size) nxt = src.d[i + 1];
+    }
+    if (i == src.size - 1) break;
+    if (dx2 < __fadd_rn(rmin_next(cur), rmax_prev(nxt))) {
+      if (i != lastidx) { dst.d[out++] = cur; lastidx = i; }
+    } else {
+      if (i + 1 != lastidx) { dst.d[out++] = nxt; lastidx = i + 1; }
+    }
+  }
+  if (lastidx != src.size - 1) dst.d[out++] = src.d[src.size - 1];
+  dst.size = out;
+}
+
+// WQSummary::SetCombine followed by FixError
+__device__ void s_combine(Summary& dst, const Summary& sa, const Summary& sb) {
+  if (sa.size == 0) { s_copy(dst, sb); return; }
+  if (sb.size == 0) { s_copy(dst, sa); return; }
+  int ia = 0, ib = 0, o = 0;
+  float aprev = 0.f, bprev = 0.f;
+  float4 a = sa.d[0], b = sb.d[0];
+  while (ia < sa.size && ib < sb.size) {
+    float4 r;
+    if (a.w == b.w) {
+      r = make_float4(__fadd_rn(a.x, b.x), __fadd_rn(a.y, b.y), __fadd_rn(a.z, b.z), a.w);
+      aprev = rmin_next(a); bprev = rmin_next(b);
+      ++ia; ++ib;
+      if (ia < sa.size) a = sa.d[ia];
+      if (ib < sb.size) b = sb.d[ib];
+    } else if (a.w < b.w) {
+      r = make_float4(__fadd_rn(a.x, bprev), __fadd_rn(a.y, rmax_prev(b)), a.z, a.w);
+      aprev = rmin_next(a);
+      ++ia;
+      if (ia < sa.size) a = sa.d[ia];
+    } else {
+      r = make_float4(__fadd_rn(b.x, aprev), __fadd_rn(b.y, rmax_prev(a)), b.z, b.w);
+      bprev = rmin_next(b);
+      ++ib;
+      if (ib < sb.size) b = sb.d[ib];
+    }
+    dst.d[o++] = r;
+  }
+  if (ia < sa.size) {
+    float brmax = sb.d[sb.size - 1].y;
+    for (; ia < sa.size; ++ia) { float4 e = sa.d[ia]; dst.d[o++] = make_float4(__fadd_rn(e.x, bprev), __fadd_rn(e.y, brmax), e.z, e.w); }
+  }
+  if (ib < sb.size) {
+    float armax = sa.d[sa.size - 1].y;
+    for (; ib < sb.size; ++ib) { float4 e = sb.d[ib]; dst.d[o++] = make_float4(__fadd_rn(e.x, aprev), __fadd_rn(e.y, armax), e.z, e.w); }
+  }
+  dst.size = o;
+  float prev_rmin = 0.f, prev_rmax = 0.f;   // FixError
+  for (int i = 0; i < o; ++i) {
+    float4 e = dst.d[i];
+    bool dirty = false;
+    if (e.x < prev_rmin) { e.x = prev_rmin; dirty = true; } else prev_rmin = e.x;
+    if (e.y < prev_rmax) { e.y = prev_rmax; dirty = true; }
+    float rn = __fadd_rn(e.x, e.z);
+    if (e.y < rn) { e.y = rn; dirty = true; }
+    prev_rmax = e.y;
+    if (dirty) dst.d[i] = e;
+  }
+}
+
+__device__ __forceinline__ uint32_t ordered_bits(float v) {
+  uint32_t b = __float_as_uint(v);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float unordered_bits(uint32_t o) {
+  uint32_t b = (o & 0x80000000u) ? (o & 0x7fffffffu) : ~o;
+  return __uint_as_float(b);
+}
+
+// CTA-wide bitonic sort of n2 (power of two) 64-bit keys living in global memory (L2 resident).
+__device__ void cta_sort(unsigned long long* keys, int n2) {
+  for (int k = 2; k <= n2; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int t = threadIdx.x; t < (n2 >> 1); t += blockDim.x) {
+        int i = ((t / j) * (j << 1)) + (t % j);
+        int l = i + j;
+        bool up = (i & k) == 0;
+        unsigned long long a = keys[i], b = keys[l];
+        if ((a > b) == up) { keys[i] = b; keys[l] = a; }
+      }
+      __syncthreads();
+    }
+  }
+}
+
+// Queue::MakeSummary on sorted keys (value in the high word, weight in the low word)
+__device__ void make_summary(const unsigned long long* keys, int qtail, Summary& out) {
+  int o = 0;
+  float wsum = 0.f;
+  int i = 0;
+  while (i < qtail) {
+    unsigned long long kk = keys[i];
+    float v = unordered_bits((uint32_t)(kk >> 32));
+    float w = (float)(uint32_t)kk;
+    int j = i + 1;
+    while (j < qtail) {
+      unsigned long long k2 = keys[j];
+      float v2 = unordered_bits((uint32_t)(k2 >> 32));
+      if (!(v2 == v)) break;
+      w = __fadd_rn(w, (float)(uint32_t)k2);
+      ++j;
+    }
+    out.d[o++] = make_float4(wsum, __fadd_rn(wsum, w), w, v);
+    wsum = __fadd_rn(wsum, w);
+    i = j;
+  }
+  out.size = o;
+}
+
+__device__ __forceinline__ int next_pow2(int v) { int p = 2; while (p < v) p <<= 1; return p; }
+
+__global__ void __launch_bounds__(kSketchThreads)
+k_sketch_cuts(const float* __restrict__ X, long long ldx, int f, int nfold,
+              const uint32_t* const* __restrict__ fold_rows, const long long* __restrict__ fold_ntrain,
+              SketchPlan plan, const int* __restrict__ fold_limit, unsigned long long* __restrict__ key_arena,
+              float4* __restrict__ entry_arena,
+              float* __restrict__ cuts_out, int* __restrict__ ncuts_out, int stream0) {
+  const int stream = blockIdx.x + stream0;
+  const int k = stream / f, j = stream % f;
+  const long long n = fold_ntrain[k];
+  const uint32_t* rows = fold_rows[k];
+  const int L = fold_limit[k], qcap = 2 * L;
+  unsigned long long* keys = key_arena + (size_t)blockIdx.x * plan.keys_per_stream;
+  float4* ent = entry_arena + (size_t)blockIdx.x * plan.entries_per_stream;
+  const int buf_cap = plan.buf_cap;   // >= 2 * L + 2 for every fold
+  Summary temp = { ent, 0 }, out = { ent + buf_cap, 0 }, red = { ent + 2 * buf_cap, 0 };
+  float4* level_space = ent + 3 * buf_cap;
+  float* cuts = cuts_out + (size_t)stream * kBins;
+
+  __shared__ float sv[kSketchThreads];
+  __shared__ int warp_tot[kSketchThreads / 32];
+  __shared__ int level_size[40];
+  __shared__ int levels_in_use;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+
+  if (tid == 0) { levels_in_use = 0; for (int l = 0; l < 40; ++l) level_size[l] = 0; }
+  for (int i = tid; i < plan.keys_per_stream; i += blockDim.x) keys[i] = 0ull;
+  __syncthreads();
+
+  if (n == 0) {   // empty column: MakeCuts' "Empty column" branch
+    if (tid == 0) { cuts[0] = __fadd_rn(1e-5f, __fadd_rn(fabsf(1e-5f), 1e-5f)); ncuts_out[stream] = 1; }
+    return;
+  }
+
+  long long pos = 0;
+  long long runs_done = 0, chunk_base = 0;
+  float lastv = 0.f;
+  while (pos < n) {
+    // ---- queue fill: QuantileSketchTemplate::Push as a run-length scan over one tile of rows
+    long long i = pos + tid;
+    bool have = i < n;
+    float v = have ? X[(size_t)rows[i] * (size_t)ldx + j] : 0.f;
+    sv[tid] = v;
+    __syncthreads();
+    float prev = tid ? sv[tid - 1] : lastv;
+    int flag = have && (i == 0 || v != prev);
+    int inc = flag;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { int t = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += t; }
+    if (lane == 31) warp_tot[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+      int t = warp_tot[lane];
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) { int u = __shfl_up_sync(0xffffffffu, t, d); if (lane >= d) t += u; }
+      warp_tot[lane] = t;
+    }
+    __syncthreads();
+    if (wid) inc += warp_tot[wid - 1];
+    long long slot = runs_done + inc - 1 - chunk_base;
+    bool in_chunk = have && slot < qcap;
+    if (in_chunk) atomicAdd(&keys[slot], (flag ? ((unsigned long long)ordered_bits(v) << 32) : 0ull) + 1ull);
+    int consumed = __syncthreads_count(in_chunk);
+    int flags_consumed = __syncthreads_count(in_chunk && flag);
+    int overflow = __syncthreads_or(have && !in_chunk);
+    if (consumed > 0) lastv = sv[consumed - 1];
+    pos += consumed;
+    runs_done += flags_consumed;
+    __syncthreads();   // sv is rewritten by the next tile
+    if (overflow) {
+      // ---- queue full and the next value differs: MakeSummary + PushTemp
+      const int n2 = next_pow2(qcap);
+      for (int t = qcap + tid; t < n2; t += blockDim.x) keys[t] = ~0ull;
+      __syncthreads();
+      cta_sort(keys, n2);
+      if (tid == 0) {
+        make_summary(keys, qcap, temp);
+        for (int l = 1;; ++l) {   // QuantileSketchTemplate::PushTemp
+          if (l + 1 > levels_in_use) levels_in_use = l + 1;
+          Summary lv = { level_space + (size_t)l * L, level_size[l] };
+          if (lv.size == 0) {
+            s_prune(lv, temp, L);
+            level_size[l] = lv.size;
+            break;
+          }
+          Summary l0 = { level_space, 0 };
+          s_prune(l0, temp, L);
+          s_combine(temp, l0, lv);
+          if (temp.size > L) {
+            level_size[l] = 0;
+          } else {
+            s_copy(lv, temp);
+            level_size[l] = lv.size;
+            break;
+          }
+        }
+      }
+      __syncthreads();
+      for (int t = tid; t < n2; t += blockDim.x) keys[t] = 0ull;
+      chunk_base += qcap;
+      __syncthreads();
+    }
+  }
+  // ---- QuantileSketchTemplate::GetSummary, SketchContainerImpl::AllReduce (one worker), MakeCuts
+  const int qtail = (int)(runs_done - chunk_base);
+  const int n2 = next_pow2(qtail);
+  for (int t = qtail + tid; t < n2; t += blockDim.x) keys[t] = ~0ull;
+  __syncthreads();
+  cta_sort(keys, n2);
+  if (tid == 0) {
+    make_summary(keys, qtail, out);
+    Summary l0 = { level_space, 0 };
+    if (levels_in_use != 0) {
+      s_prune(l0, out, L);
+      for (int l = 1; l < levels_in_use; ++l) {
+        if (level_size[l] == 0) continue;
+        Summary lv = { level_space + (size_t)l * L, level_size[l] };
+        if (l0.size == 0) {
+          s_copy(l0, lv);
+        } else {
+          s_combine(out, l0, lv);
+          s_prune(l0, out, L);
+        }
+      }
+      s_copy(out, l0);
+    } else if (out.size > L) {
+      s_prune(temp, out, L);
+      s_copy(out, temp);
+    }
+    const long long inter = n < (long long)kBins * 8 ? n : (long long)kBins * 8;
+    s_prune(red, out, (int)inter);
+    const int max_num_bins = inter < kBins ? (int)inter : kBins;
+    s_prune(temp, red, max_num_bins + 1);
+    // hist_util.h AddCutPoint + the trailing sentinel of MakeCuts
+    const int required = temp.size < max_num_bins ? temp.size : max_num_bins;
+    int nc = 0;
+    for (int i2 = 1; i2 < required; ++i2) {
+      float cpt = temp.d[i2].w;
+      if (i2 == 1 || cpt > cuts[nc - 1]) cuts[nc++] = cpt;
+    }
+    float cpt = temp.d[temp.size - 1].w;
+    cuts[nc++] = __fadd_rn(cpt, __fadd_rn(fabsf(cpt), 1e-5f));
+    ncuts_out[stream] = nc;
+  }
+}
+
+// HistogramCuts::SearchBin: index of the first cut strictly greater than x, clamped to the last cut.
+__global__ void k_bin_u8(const float* __restrict__ X, long long ldx, int f, int fpad,
+                         const uint32_t* __restrict__ rows, long long n,
+                         const float* __restrict__ cuts, const int* __restrict__ ncuts, uint8_t* __restrict__ bins) {
+  const int words = fpad >> 2;
+  const long long total = n * words;
+  for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+    long long r = t / words;
+    int w = (int)(t % words);
+    const float* xr = X + (size_t)rows[r] * (size_t)ldx;
+    uint32_t packed = 0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      int j = w * 4 + q;
+      uint32_t b = 0;
+      if (j < f) {
+        const float* c = cuts + (size_t)j * kBins;
+        int nc = ncuts[j];
+        float x = xr[j];
+        int lo = 0, hi = nc;
+        while (lo < hi) { int mid = (lo + hi) >> 1; if (c[mid] > x) hi = mid; else lo = mid + 1; }
+        if (lo == nc) lo = nc - 1;
+        b = (uint32_t)lo;
+      }
+      packed |= b << (8 * q);
+    }
+    reinterpret_cast<uint32_t*>(bins)[t] = packed;
+  }
+}
+
+__global__ void k_gather_y(const float* __restrict__ y, const uint32_t* __restrict__ rows, long long n, float* __restrict__ out) {
+  for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) out[t] = y[rows[t]];
+}
+
+}  // namespace
+
+void launch_sketch(const float* X, long long ldx, int f, int nfold, const uint32_t* const* fold_rows,
+                   const long long* fold_ntrain, const SketchPlan& plan, const int* fold_limit,
+                   unsigned long long* key_arena, float4* entry_arena, float* cuts, int* ncuts, int stream0,
+                   int count, cudaStream_t s) {
+  k_sketch_cuts<<<count, kSketchThreads, 0, s>>>(X, ldx, f, nfold, fold_rows, fold_ntrain, plan, fold_limit,
+                                                 key_arena, entry_arena, cuts, ncuts, stream0);
+}
+
+void launch_bin(const float* X, long long ldx, int f, int fpad, const uint32_t* rows, long long n,
+                const float* cuts, const int* ncuts, uint8_t* bins, cudaStream_t s) {
+  long long total = n * (fpad / 4);
+  int blocks = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+  if (blocks < 1) blocks = 1;
+  k_bin_u8<<<blocks, 256, 0, s>>>(X, ldx, f, fpad, rows, n, cuts, ncuts, bins);
+}
+
+void launch_gather_y(const float* y, const uint32_t* rows, long long n, float* out, cudaStream_t s) {
+  int blocks = (int)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
+  if (blocks < 1) blocks = 1;
+  k_gather_y<<<blocks, 256, 0, s>>>(y, rows, n, out);
+}
+
+}  // namespace gt

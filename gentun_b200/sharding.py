@@ -1,0 +1,56 @@
+"""Population sharding over the GPUs of one box.
+
+The reference farms individuals out one per AMQP message (gentun/master.py:116-123) and collects
+`[i, fitness]` replies (master.py:126-129).  Here every rank (one process per GPU, torch.distributed)
+holds a replica of the binned data, evaluates a slice of the individuals, and the only collective is
+an all-gather of the fitness scalars.  Every rank runs the same seeded GA, so no genes are broadcast.
+"""
+import numpy as np
+
+
+def _dist():
+    try:
+        import torch.distributed as dist
+    except Exception:  # torch not importable: single-process use
+        return None
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+        return dist
+    return None
+
+
+def shard_plan(depths, world_size):
+    """Deal individuals to ranks: deepest first, round-robin, so every rank gets a similar cost mix.
+    Returns a list (per rank) of index arrays into the population."""
+    order = np.argsort(-np.asarray(depths, dtype=np.float64), kind="stable")
+    return [order[r::world_size] for r in range(world_size)]
+
+
+def evaluate_sharded(engine, genes_list, params, local_eval=None):
+    """Fitness vector for genes_list, identical on every rank."""
+    n = len(genes_list)
+    if local_eval is None:
+        def local_eval(sub):
+            return engine.evaluate(sub, **params)[0]
+    dist = _dist()
+    if dist is None:
+        return np.asarray(local_eval(list(genes_list)), dtype=np.float64)
+    import torch
+    world, rank = dist.get_world_size(), dist.get_rank()
+    plan = shard_plan([g["max_depth"] for g in genes_list], world)
+    mine = plan[rank]
+    local = np.asarray(local_eval([genes_list[i] for i in mine]), dtype=np.float64) if len(mine) else np.zeros(0)
+    width = max(len(p) for p in plan)
+    backend = dist.get_backend()
+    dev = torch.device("cuda", torch.cuda.current_device()) if backend == "nccl" else torch.device("cpu")
+    send = torch.full((width,), float("nan"), dtype=torch.float64, device=dev)
+    if len(mine):
+        send[:len(mine)] = torch.from_numpy(local).to(dev)
+    recv = torch.empty((world * width,), dtype=torch.float64, device=dev)
+    dist.all_gather_into_tensor(recv, send)
+    table = recv.cpu().numpy().reshape(world, width)
+    out = np.full(n, np.nan)
+    for r in range(world):
+        out[plan[r]] = table[r, :len(plan[r])]
+    if np.isnan(out).any():
+        raise RuntimeError("gentun_b200: fitness all-gather left %d individuals unevaluated" % int(np.isnan(out).sum()))
+    return out
