@@ -1,0 +1,303 @@
+"""Parity of the CUDA path (called through the C ABI, libgentun_b200.so) against the CPU oracle on the
+same inputs.  Bit-exact for folds, cut points, bin indices and row partitions; 1e-4 relative for the
+CV fitness (north_star), with the tolerance written at each assert."""
+import contextlib
+import io
+import random
+
+import numpy as np
+import pytest
+
+from oracle import orc
+from tests.synth import make_dataset
+
+pytestmark = pytest.mark.gpu
+
+REL_TOL = 1e-4   # north_star: per-individual CV fitness within 1e-4 relative
+
+
+def rel(a, b):
+    return abs(a - b) / max(abs(b), 1e-12)
+
+
+@pytest.fixture(scope="module")
+def wine_np(wine):
+    x, y = wine
+    return np.ascontiguousarray(x.values, dtype=np.float32), np.ascontiguousarray(y.values, dtype=np.float32)
+
+
+@pytest.fixture(scope="module")
+def wine_pair(wine_np):
+    from gentun_b200.engine import Engine
+    x, y = wine_np
+    eng = Engine(x, y)
+    ctx = orc.Context(x, y, 3)
+    yield eng, ctx
+    eng.close()
+    ctx.close()
+
+
+@pytest.fixture(scope="module")
+def synth_pair():
+    from gentun_b200.engine import Engine
+    x, y = make_dataset(60000, 20, seed=1003)
+    eng = Engine(x, y)
+    ctx = orc.Context(x, y, 4)
+    yield eng, ctx, x, y
+    eng.close()
+    ctx.close()
+
+
+def genes(**kw):
+    g = {'eta': 0.3, 'min_child_weight': 1, 'max_depth': 6, 'gamma': 0.0, 'max_delta_step': 0, 'subsample': 1.0,
+         'colsample_bytree': 1.0, 'colsample_bylevel': 1.0, 'lambda': 1.0, 'alpha': 0.0, 'scale_pos_weight': 1.0}
+    g.update(kw)
+    return g
+
+
+def test_library_is_the_cuda_build():
+    from gentun_b200 import engine
+    lib = engine.load_library()
+    assert lib.gt_version() >= 100
+
+
+# ---------------------------------------------------------------- X1-X3: folds, cuts, bins (bit-exact)
+def test_folds_bit_exact_wine(wine_pair):
+    eng, ctx = wine_pair
+    for k in range(3):
+        tr, te = eng.fold_rows(3, k)
+        assert np.array_equal(tr, ctx.train_rows(k))
+        assert np.array_equal(te, ctx.test_rows(k))
+    np.random.seed(0)
+    perm = np.random.permutation(4898)
+    assert np.array_equal(eng.fold_rows(3, 0)[1], perm[:1633])
+
+
+def test_cuts_and_bins_bit_exact_wine(wine_pair):
+    eng, ctx = wine_pair
+    for k in range(3):
+        cu, nc = eng.cuts(3, k)
+        ocu, onc = ctx.cuts(k)
+        assert np.array_equal(nc, onc)
+        for j in range(eng.f):
+            assert np.array_equal(cu[j, :nc[j]].view(np.uint32), ocu[j, :nc[j]].view(np.uint32)), (k, j)
+        assert np.array_equal(eng.bins(3, k), ctx.all_bins(k))
+
+
+def test_cuts_and_bins_bit_exact_multilevel_sketch(synth_pair):
+    """45000 train rows per fold > 2 * limit_size: the sketch flushes its queue several times and the
+    summary hierarchy (SetPrune / SetCombine across levels) is exercised."""
+    eng, ctx, _, _ = synth_pair
+    for k in range(4):
+        cu, nc = eng.cuts(4, k)
+        ocu, onc = ctx.cuts(k)
+        assert np.array_equal(nc, onc)
+        for j in range(eng.f):
+            assert np.array_equal(cu[j, :nc[j]].view(np.uint32), ocu[j, :nc[j]].view(np.uint32)), (k, j)
+    assert np.array_equal(eng.bins(4, 1), ctx.all_bins(1))
+
+
+def test_ragged_and_tiny_inputs():
+    from gentun_b200.engine import Engine
+    for n, f, nfold in [(53, 3, 5), (1001, 33, 3), (257, 1, 2)]:
+        x, y = make_dataset(n, f, seed=n)
+        x[:, 0] = np.round(x[:, 0]) + 0.0      # heavy ties (+0.0 folds -0.0 into +0.0: equal cuts, one spelling)
+        if f > 2:
+            x[:, 2] = 1.5                      # constant column
+        eng = Engine(x, y)
+        ctx = orc.Context(x, y, nfold)
+        for k in range(nfold):
+            assert eng.fold_sizes(nfold, k) == (ctx.ntrain(k), ctx.ntest(k))
+            cu, nc = eng.cuts(nfold, k)
+            ocu, onc = ctx.cuts(k)
+            assert np.array_equal(nc, onc)
+            for j in range(f):
+                assert np.array_equal(cu[j, :nc[j]].view(np.uint32), ocu[j, :nc[j]].view(np.uint32))
+            assert np.array_equal(eng.bins(nfold, k), ctx.all_bins(k))
+        g = genes(max_depth=4)
+        fit, rounds = eng.evaluate([g], nfold=nfold, num_boost_round=8)
+        want = ctx.cv(g, orc.make_opts(nfold=nfold, num_boost_round=8))
+        assert rel(fit[0], want["fitness"]) < REL_TOL
+        eng.close()
+        ctx.close()
+
+
+# ---------------------------------------------------------------- X4-X9: boosting, metric, early stop
+GENE_SETS = [
+    genes(),
+    genes(max_depth=3, eta=0.1),
+    genes(max_depth=10, eta=0.05, min_child_weight=0),
+    genes(max_depth=8, gamma=0.7, min_child_weight=5),
+    genes(max_depth=5, alpha=1.5, **{'lambda': 4.0}),
+    genes(max_depth=7, max_delta_step=1, alpha=0.3),
+    genes(max_depth=4, max_delta_step=3, min_child_weight=10, eta=1.0),
+    genes(max_depth=6, scale_pos_weight=3.5, gamma=9.5),
+]
+
+
+def test_fitness_and_trace_parity_wine(wine_pair):
+    eng, ctx = wine_pair
+    fit, rounds, extra = eng.evaluate(GENE_SETS, trace=True, nfold=3, num_boost_round=25)
+    for i, g in enumerate(GENE_SETS):
+        want = ctx.cv(g, orc.make_opts(nfold=3, num_boost_round=25), trace=True)
+        assert rounds[i] == want["rounds"] == 25
+        assert rel(fit[i], want["fitness"]) < REL_TOL, (i, fit[i], want["fitness"])
+        np.testing.assert_allclose(extra["trace"][i, :25], want["trace"], rtol=REL_TOL)
+
+
+def test_tree_structure_and_row_partitions(wine_pair):
+    eng, ctx = wine_pair
+    gs = [genes(max_depth=5), genes(max_depth=8, min_child_weight=0, eta=0.1)]
+    R = 4
+    fit, rounds, extra = eng.evaluate(gs, tree_rounds=R, rows_round=R - 1, nfold=3, num_boost_round=R)
+    same = total = 0
+    for i, g in enumerate(gs):
+        want = ctx.cv(g, orc.make_opts(nfold=3, num_boost_round=R), trees_rounds=R)
+        for k in range(3):
+            bins = ctx.train_bins(k)
+            for r in range(R):
+                mine, ref = extra["trees"][i, k, r], want["trees"][k, r]
+                exists = ref["feat"] != -2
+                total += int(exists.sum())
+                same += int(((mine["feat"] == ref["feat"]) & (mine["bin"] == ref["bin"]))[exists].sum())
+                # round 0 starts from identical gradients: structure must be identical
+                if r == 0:
+                    assert np.array_equal(mine["feat"], ref["feat"]) and np.array_equal(mine["bin"], ref["bin"])
+                    leaf = ref["feat"] == -1
+                    # leaf values differ only by the 2^-19 fixed-point quantisation of the gradients
+                    np.testing.assert_allclose(mine["value"][leaf], ref["value"][leaf], rtol=2e-4, atol=2e-6)
+            # row partitions of the last dumped tree: every node that owns a segment holds exactly the
+            # rows that reach it, in ascending slice-local order (stable partition from the identity)
+            tree = extra["trees"][i, k, R - 1]
+            if not (np.array_equal(tree["feat"], want["trees"][k, R - 1]["feat"]) and
+                    np.array_equal(tree["bin"], want["trees"][k, R - 1]["bin"])):
+                continue
+            D = g["max_depth"]
+            members = {0: np.arange(ctx.ntrain(k))}
+            for nid in range(2 ** D - 1):
+                if nid not in members or tree["feat"][nid] < 0:
+                    continue
+                rows = members[nid]
+                left = bins[rows, tree["feat"][nid]] <= tree["bin"][nid]
+                members[2 * nid + 1], members[2 * nid + 2] = rows[left], rows[~left]
+            nr, rs = extra["node_rows"][i, k], extra["row_sets"][i, k]
+            checked = 0
+            for nid, rows in members.items():
+                depth = int(np.floor(np.log2(nid + 1)))
+                if depth >= D:      # children of the last evaluated level are never partitioned
+                    continue
+                # the two row-set buffers ping-pong level by level, so a split node's segment is later
+                # reused by its grandchildren; leaves and the deepest evaluated level stay intact
+                if not (tree["feat"][nid] == -1 or depth == D - 1):
+                    continue
+                seg = rs[nr["buf"][nid], nr["begin"][nid]: nr["begin"][nid] + nr["count"][nid]]
+                assert np.array_equal(seg.astype(np.int64), rows), (i, k, nid)
+                checked += 1
+            assert checked >= 3
+    assert same / total > 0.98, (same, total)
+
+
+def test_early_stopping_matches(wine_pair):
+    eng, ctx = wine_pair
+    gs = [genes(eta=0.9, max_depth=8), genes(eta=0.5)]
+    fit, rounds = eng.evaluate(gs, nfold=3, num_boost_round=400, early_stopping_rounds=15)
+    for i, g in enumerate(gs):
+        want = ctx.cv(g, orc.make_opts(nfold=3, num_boost_round=400, early_stopping_rounds=15))
+        assert want["stopped_early"]
+        assert rounds[i] == want["rounds"]
+        assert rel(fit[i], want["fitness"]) < REL_TOL
+
+
+def test_sampling_genes_match_oracle_definition(synth_pair):
+    """subsample / colsample_* use the counter-based generator both sides define identically."""
+    eng, ctx, _, _ = synth_pair
+    gs = [genes(subsample=0.6, max_depth=5), genes(colsample_bytree=0.5, colsample_bylevel=0.7, max_depth=5),
+          genes(subsample=0.9, colsample_bytree=0.0002, max_depth=4), genes(subsample=0.0, max_depth=3)]
+    fit, rounds = eng.evaluate(gs, nfold=4, num_boost_round=10)
+    for i, g in enumerate(gs):
+        want = ctx.cv(g, orc.make_opts(nfold=4, num_boost_round=10))
+        assert rel(fit[i], want["fitness"]) < REL_TOL, (i, fit[i], want["fitness"])
+
+
+def test_regression_parity_synthetic_deep(synth_pair):
+    eng, ctx, _, _ = synth_pair
+    gs = [genes(max_depth=10, eta=0.2, min_child_weight=0), genes(max_depth=6, eta=0.3, max_delta_step=2)]
+    fit, rounds = eng.evaluate(gs, nfold=4, num_boost_round=12)
+    for i, g in enumerate(gs):
+        want = ctx.cv(g, orc.make_opts(nfold=4, num_boost_round=12))
+        assert rel(fit[i], want["fitness"]) < REL_TOL, (i, fit[i], want["fitness"])
+
+
+def test_logistic_logloss_parity():
+    from gentun_b200.engine import Engine
+    x, y = make_dataset(30000, 12, seed=1004, classification=True)
+    eng = Engine(x, y)
+    ctx = orc.Context(x, y, 3)
+    gs = [genes(max_depth=5, scale_pos_weight=2.5), genes(max_depth=7, eta=0.1, scale_pos_weight=0.4, max_delta_step=1)]
+    params = dict(objective="binary:logistic", eval_metric="logloss", nfold=3, num_boost_round=15)
+    fit, rounds = eng.evaluate(gs, **params)
+    for i, g in enumerate(gs):
+        want = ctx.cv(g, orc.make_opts(**params))
+        assert rel(fit[i], want["fitness"]) < REL_TOL, (i, fit[i], want["fitness"])
+    eng.close()
+    ctx.close()
+
+
+def test_deterministic_and_wave_independent(wine_np):
+    """Integer histograms make the result independent of scheduling and of how individuals are batched."""
+    from gentun_b200.engine import Engine
+    x, y = wine_np
+    eng = Engine(x, y)
+    a, _ = eng.evaluate(GENE_SETS, nfold=3, num_boost_round=10)
+    b, _ = eng.evaluate(GENE_SETS, nfold=3, num_boost_round=10)
+    assert np.array_equal(a, b)
+    small = Engine(x, y, mem_budget_bytes=400 << 20)    # forces several waves
+    c, _ = small.evaluate(GENE_SETS, nfold=3, num_boost_round=10)
+    assert small.stats()["waves"] > 1
+    assert np.array_equal(a, c)
+    one, _ = eng.evaluate(GENE_SETS[3:4], nfold=3, num_boost_round=10)
+    assert one[0] == a[3]
+    eng.close()
+    small.close()
+
+
+def test_bad_genes_are_rejected(wine_pair):
+    eng, _ = wine_pair
+    with pytest.raises(ValueError):
+        eng.evaluate([genes(max_depth=11)], nfold=3, num_boost_round=2)
+    with pytest.raises(ValueError):
+        eng.evaluate([genes(subsample=1.5)], nfold=3, num_boost_round=2)
+    with pytest.raises(ValueError):
+        eng.evaluate([genes(eta=float("nan"))], nfold=3, num_boost_round=2)
+    with pytest.raises(ValueError):
+        eng.evaluate([genes()], nfold=1, num_boost_round=2)
+
+
+# ---------------------------------------------------------------- the drop-in API on the GPU
+def test_xgboost_model_and_population_drop_in(wine):
+    """The reference's tests/test_xgboost_model.py and tests/test_wine-quality.py flows (shortened)."""
+    import gentun_b200 as gentun
+    x, y = wine                                   # pandas DataFrame / Series, as the scripts load them
+    g = genes()
+    model = gentun.XgboostModel(x, y, g, nfold=3, num_boost_round=20)
+    got = model.cross_validate()
+    ctx = orc.Context(x.values, y.values, 3)
+    want = ctx.cv(g, orc.make_opts(nfold=3, num_boost_round=20))["fitness"]
+    assert rel(got, want) < REL_TOL
+    random.seed(11)
+    with contextlib.redirect_stdout(io.StringIO()):
+        pop = gentun.Population(gentun.XgboostIndividual, x, y, size=6, maximize=False,
+                                additional_parameters={'nfold': 3, 'num_boost_round': 10})
+        ga = gentun.GeneticAlgorithm(pop, tournament_size=3)
+        ga.run(2)
+    best = pop.get_fittest()
+    assert best.get_fitness() == min(pop[i].get_fitness() for i in range(6))
+    ok = 0
+    for i in range(6):
+        gi = pop[i].get_genes()
+        w = ctx.cv(gi, orc.make_opts(nfold=3, num_boost_round=10))["fitness"]
+        assert rel(pop[i].get_fitness(), w) < REL_TOL
+        ok += 1
+    assert ok == 6
+    gentun.clear_engines()
+    ctx.close()
