@@ -213,46 +213,70 @@ __global__ void __launch_bounds__(256) k_plan_hist(Wave w, int level) {
   } else {
     for (int q = threadIdx.x; q < kMaskWords; q += blockDim.x) js.lmask[q] = s_in[q];
   }
-  if (threadIdx.x != 0) return;
   // work items: histogram chunks of the nodes to build, (built, sibling) pairs to evaluate
   Node* nodes = w.nodes + (size_t)j * kNodeCap;
   HistItem* items = w.hitems + (size_t)j * w.hist_cap;
   PairRec* pairs = w.pairs + (size_t)j * w.pair_cap;
   int* zl = w.zlist + (size_t)j * w.hist_cap;
-  int ni = 0, np = 0, nz = 0;
-  unsigned long long rows_total = 0, built = 0;
-  if (level == 0) {
-    const Node& r = nodes[0];
-    int chunks = (int)((r.cnt + kHistRows - 1) / kHistRows); if (chunks < 1) chunks = 1;
-    for (int c = 0; c < chunks && ni < w.hist_cap; ++c) {
-      uint32_t b = (uint32_t)c * kHistRows;
-      uint32_t cnt = r.cnt > b ? (r.cnt - b < (uint32_t)kHistRows ? r.cnt - b : (uint32_t)kHistRows) : 0u;
-      items[ni++] = HistItem{0, b, cnt, (chunks > 1 ? 1 : 0) | (r.buf << 1)};
-    }
-    if (chunks > 1) zl[nz++] = 0;
-    pairs[np++] = PairRec{-1, 0};
-    rows_total += r.cnt; built += 1;
-  } else {
-    const int first = level_first(level - 1), last = level_first(level);
-    for (int p = first; p < last; ++p) {
+  __shared__ int s_scan[3][256];
+  __shared__ unsigned long long s_rows;
+  if (threadIdx.x == 0) s_rows = 0ull;
+  // each thread owns up to two parents (2 * 256 >= 2^(kMaxDepth - 1))
+  const int n_par = level == 0 ? 1 : (1 << (level - 1));
+  const int first = level == 0 ? 0 : level_first(level - 1);
+  int bnode[2], chunks[2];
+  for (int s2 = 0; s2 < 2; ++s2) {
+    const int pi = 2 * threadIdx.x + s2;
+    bnode[s2] = -1; chunks[s2] = 0;
+    if (pi >= n_par) continue;
+    if (level == 0) {
+      bnode[s2] = 0;
+    } else {
+      const int p = first + pi;
       if (nodes[p].state != kSplit) continue;
       const int l = 2 * p + 1, r = 2 * p + 2;
-      const int bnode = nodes[l].cnt <= nodes[r].cnt ? l : r;
-      const Node& bn = nodes[bnode];
-      int chunks = (int)((bn.cnt + kHistRows - 1) / kHistRows); if (chunks < 1) chunks = 1;
-      for (int c = 0; c < chunks && ni < w.hist_cap; ++c) {
-        uint32_t b = (uint32_t)c * kHistRows;
-        uint32_t cnt = bn.cnt > b ? (bn.cnt - b < (uint32_t)kHistRows ? bn.cnt - b : (uint32_t)kHistRows) : 0u;
-        items[ni++] = HistItem{bnode, bn.begin + b, cnt, (chunks > 1 ? 1 : 0) | (bn.buf << 1)};
-      }
-      if (chunks > 1 && nz < w.hist_cap) zl[nz++] = bnode;
-      if (np < w.pair_cap) pairs[np++] = PairRec{p, bnode == r ? 1 : 0};
-      rows_total += bn.cnt; built += 1;
+      bnode[s2] = nodes[l].cnt <= nodes[r].cnt ? l : r;
     }
+    const uint32_t cnt = nodes[bnode[s2]].cnt;
+    chunks[s2] = (int)((cnt + kHistRows - 1) / kHistRows);
+    if (chunks[s2] < 1) chunks[s2] = 1;
   }
-  js.n_hist_items = ni; js.n_pairs = np; js.n_zero = nz;
-  if (rows_total) atomicAdd(&w.counters[0], rows_total);
-  if (built) atomicAdd(&w.counters[1], built);
+  __syncthreads();   // s_rows initialised
+  int v[3] = {chunks[0] + chunks[1], (bnode[0] >= 0) + (bnode[1] >= 0), (chunks[0] > 1) + (chunks[1] > 1)};
+  for (int q = 0; q < 3; ++q) s_scan[q][threadIdx.x] = v[q];
+  __syncthreads();
+  for (int d = 1; d < 256; d <<= 1) {   // Hillis-Steele inclusive scan of the three counters
+    int t[3];
+    for (int q = 0; q < 3; ++q) t[q] = threadIdx.x >= d ? s_scan[q][threadIdx.x - d] : 0;
+    __syncthreads();
+    for (int q = 0; q < 3; ++q) s_scan[q][threadIdx.x] += t[q];
+    __syncthreads();
+  }
+  int ni = s_scan[0][threadIdx.x] - v[0], np = s_scan[1][threadIdx.x] - v[1], nz = s_scan[2][threadIdx.x] - v[2];
+  unsigned long long rows_mine = 0;
+  for (int s2 = 0; s2 < 2; ++s2) {
+    if (bnode[s2] < 0) continue;
+    const Node& bn = nodes[bnode[s2]];
+    for (int c = 0; c < chunks[s2]; ++c, ++ni) {
+      if (ni >= w.hist_cap) break;
+      const uint32_t b = (uint32_t)c * kHistRows;
+      const uint32_t cnt = bn.cnt > b ? (bn.cnt - b < (uint32_t)kHistRows ? bn.cnt - b : (uint32_t)kHistRows) : 0u;
+      items[ni] = HistItem{bnode[s2], bn.begin + b, cnt, (chunks[s2] > 1 ? 1 : 0) | ((int)bn.buf << 1)};
+    }
+    if (chunks[s2] > 1) { if (nz < w.hist_cap) zl[nz] = bnode[s2]; ++nz; }
+    if (np < w.pair_cap) pairs[np] = level == 0 ? PairRec{-1, 0} : PairRec{(bnode[s2] - 1) >> 1, (bnode[s2] & 1) ? 0 : 1};
+    ++np;
+    rows_mine += bn.cnt;
+  }
+  if (rows_mine) atomicAdd(&s_rows, rows_mine);
+  __syncthreads();
+  if (threadIdx.x == 255) {
+    js.n_hist_items = min(s_scan[0][255], w.hist_cap);
+    js.n_pairs = min(s_scan[1][255], w.pair_cap);
+    js.n_zero = min(s_scan[2][255], w.hist_cap);
+    if (s_rows) atomicAdd(&w.counters[0], s_rows);
+    if (s_scan[1][255]) atomicAdd(&w.counters[1], (unsigned long long)s_scan[1][255]);
+  }
 }
 
 __device__ __forceinline__ HistEntry* node_hist(const Wave& w, const JobParams& jp, int level, int node) {
@@ -282,51 +306,83 @@ __device__ __forceinline__ uint4 ld_stream(const uint4* p) {
   return r;
 }
 
-__global__ void __launch_bounds__(kHistThreads) k_hist(Wave w, int level) {
+struct HistStage { uint4 b0, b1; int2 g0, g1; };
+
+// 32 rows of a warp's stripe: two sub-batches of 16 rows, lane = (row slot rl, 16-byte half)
+__device__ __forceinline__ void hist_load(HistStage& st, uint32_t myrow, int rl, const uint8_t* __restrict__ bins_half,
+                                          const int2* __restrict__ gq, int fpad) {
+  const uint32_t r0 = __shfl_sync(0xffffffffu, myrow, rl), r1 = __shfl_sync(0xffffffffu, myrow, 16 + rl);
+  // rows past the end of the item read row 0 and add a zero gradient: no predicate in the hot loop
+  const bool v0 = r0 != 0xffffffffu, v1 = r1 != 0xffffffffu;
+  const uint32_t a0 = v0 ? r0 : 0u, a1 = v1 ? r1 : 0u;
+  st.b0 = ld_stream(reinterpret_cast<const uint4*>(bins_half + (size_t)a0 * fpad));
+  st.b1 = ld_stream(reinterpret_cast<const uint4*>(bins_half + (size_t)a1 * fpad));
+  const int2 z = make_int2(0, 0);
+  st.g0 = v0 ? gq[a0] : z;
+  st.g1 = v1 ? gq[a1] : z;
+}
+
+__device__ __forceinline__ void hist_accumulate(const uint4 v, const int2 g2, int q, int rb, const int (&cs)[16], char* shb) {
+  // rotate the 16 bytes right by rl bytes: word rotation by q = rl / 4, then funnel shift by rb bits
+  const uint32_t u0 = q == 0 ? v.x : q == 1 ? v.y : q == 2 ? v.z : v.w;
+  const uint32_t u1 = q == 0 ? v.y : q == 1 ? v.z : q == 2 ? v.w : v.x;
+  const uint32_t u2 = q == 0 ? v.z : q == 1 ? v.w : q == 2 ? v.x : v.y;
+  const uint32_t u3 = q == 0 ? v.w : q == 1 ? v.x : q == 2 ? v.y : v.z;
+  uint32_t r[4];
+  r[0] = __funnelshift_r(u0, u1, rb);
+  r[1] = __funnelshift_r(u1, u2, rb);
+  r[2] = __funnelshift_r(u2, u3, rb);
+  r[3] = __funnelshift_r(u3, u0, rb);
+#pragma unroll
+  for (int s = 0; s < 16; ++s) {
+    const uint32_t bin = __byte_perm(r[s >> 2], 0u, 0x4440u + (uint32_t)(s & 3));
+    char* cell = shb + (bin * (kLanes * 4u) + (uint32_t)cs[s]);
+    atomicAdd(reinterpret_cast<int*>(cell), g2.x);
+    atomicAdd(reinterpret_cast<int*>(cell + kBins * kLanes * 4), g2.y);
+  }
+}
+
+__global__ void __launch_bounds__(kHistThreads, 3) k_hist(Wave w, int level) {
   const int j = blockIdx.y;
   const JobState& js = w.js[j];
   const int item_idx = blockIdx.x / w.groups, grp = blockIdx.x % w.groups;
   if (item_idx >= js.n_hist_items) return;
-  const JobParams jp = w.jp[j];
+  const JobParams& jp = w.jp[j];
   const HistItem it = w.hitems[(size_t)j * w.hist_cap + item_idx];
   extern __shared__ int sh[];
   int* sh_g = sh;
   int* sh_h = sh + kBins * kLanes;
   for (int i = threadIdx.x; i < 2 * kBins * kLanes / 4; i += kHistThreads) reinterpret_cast<int4*>(sh)[i] = make_int4(0, 0, 0, 0);
   __syncthreads();
-  const uint8_t* bins = w.folds[jp.fold].bins + (size_t)grp * kLanes;
-  const uint32_t* ridx = w.ridx + ((size_t)j * 2 + (size_t)((it.flags >> 1) & 1)) * w.nt_stride + it.begin;
-  const int2* gq = w.gq + (size_t)j * w.nt_stride;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int rl = lane >> 1, half = lane & 1;
   const int q = rl >> 2, rb = (rl & 3) * 8;
-  const int fbase = half * 16;
-  const int nfeat_grp = min(kLanes, w.f - grp * kLanes);   // real features in this group
-  for (uint32_t base = (uint32_t)wid * 16u; base < it.cnt; base += (kHistThreads / 32) * 16u) {
-    const uint32_t p = base + (uint32_t)rl;
-    const bool valid = p < it.cnt;
-    uint32_t row = valid ? ridx[p] : 0u;
-    int2 g2 = valid ? gq[row] : make_int2(0, 0);
-    uint4 v = valid ? ld_stream(reinterpret_cast<const uint4*>(bins + (size_t)row * w.fpad + fbase)) : make_uint4(0, 0, 0, 0);
-    // rotate the 16 bytes right by rl bytes: word rotation by q, then funnel shift by rb bits
-    uint32_t u0 = q == 0 ? v.x : q == 1 ? v.y : q == 2 ? v.z : v.w;
-    uint32_t u1 = q == 0 ? v.y : q == 1 ? v.z : q == 2 ? v.w : v.x;
-    uint32_t u2 = q == 0 ? v.z : q == 1 ? v.w : q == 2 ? v.x : v.y;
-    uint32_t u3 = q == 0 ? v.w : q == 1 ? v.x : q == 2 ? v.y : v.z;
-    uint32_t r[4];
-    r[0] = __funnelshift_r(u0, u1, rb);
-    r[1] = __funnelshift_r(u1, u2, rb);
-    r[2] = __funnelshift_r(u2, u3, rb);
-    r[3] = __funnelshift_r(u3, u0, rb);
+  const uint8_t* bins_half = w.folds[jp.fold].bins + (size_t)grp * kLanes + half * 16;
+  const uint32_t* ridx = w.ridx + ((size_t)j * 2 + (size_t)((it.flags >> 1) & 1)) * w.nt_stride + it.begin;
+  const int2* gq = w.gq + (size_t)j * w.nt_stride;
+  const int fpad = w.fpad;
+  int cs[16];   // byte offset of this lane's feature column at unrolled step s
 #pragma unroll
-    for (int s = 0; s < 16; ++s) {
-      const uint32_t bin = (r[s >> 2] >> ((s & 3) * 8)) & 0xffu;
-      const int fl = fbase + ((s + rl) & 15);
-      if (valid && fl < nfeat_grp) {
-        const int a = (int)bin * kLanes + fl;
-        atomicAdd(&sh_g[a], g2.x);
-        atomicAdd(&sh_h[a], g2.y);
+  for (int s = 0; s < 16; ++s) cs[s] = (half * 16 + ((s + rl) & 15)) * 4;
+  char* shb = reinterpret_cast<char*>(sh);
+  constexpr uint32_t kStride = (kHistThreads / 32) * 32u;
+  uint32_t base = (uint32_t)wid * 32u;
+  if (base < it.cnt) {
+    HistStage cur, nxt;
+    uint32_t myrow = base + lane < it.cnt ? ridx[base + lane] : 0xffffffffu;
+    hist_load(cur, myrow, rl, bins_half, gq, fpad);
+    for (;;) {
+      const uint32_t nb = base + kStride;
+      const bool more = nb < it.cnt;
+      if (more) {
+        myrow = nb + lane < it.cnt ? ridx[nb + lane] : 0xffffffffu;
+        hist_load(nxt, myrow, rl, bins_half, gq, fpad);
       }
+      hist_accumulate(cur.b0, cur.g0, q, rb, cs, shb);
+      hist_accumulate(cur.b1, cur.g1, q, rb, cs, shb);
+      if (!more) break;
+      cur = nxt;
+      base = nb;
     }
   }
   __syncthreads();
@@ -344,32 +400,40 @@ __global__ void __launch_bounds__(kHistThreads) k_hist(Wave w, int level) {
 }
 
 // ------------------------------------------------------------------ X6: split enumeration
-// One CTA per (job, parent): warps = 2 children x feature groups, lane = feature.  Each lane keeps a
-// running prefix over its feature's bins (EnumerateSplit<+1>), the sibling histogram is formed on the
-// fly as parent - built, and the per-lane best candidates are merged with warp shuffles.
+// One CTA per (job, parent).  Warps = 2 children x feature groups x bin chunks, lane = feature.
+// Pass 1: every warp sums its chunk of bins (forming the sibling histogram on the fly as
+// parent - built and storing it when a later level needs it as a parent).  Pass 2: with the chunk
+// prefix from shared memory each lane runs EnumerateSplit<+1> over its bins; candidates are merged
+// with warp shuffles, then across warps.
 struct Cand { float chg; int f; int b; long long GL, HL; };
 
-__device__ __forceinline__ bool better(float chg, int f, float ochg, int of) {
-  // SplitEntry::NeedReplace with ascending feature order: strictly greater, ties keep the lower feature
-  return (chg > ochg) || (chg == ochg && f >= 0 && (of < 0 || f < of));
+__device__ __forceinline__ bool better(float chg, int f, int b, float ochg, int of, int ob) {
+  // SplitEntry::NeedReplace under an ascending (feature, bin) scan: strictly greater gain wins,
+  // equal gain keeps the earlier (feature, bin)
+  if (chg > ochg) return true;
+  if (chg < ochg || f < 0) return false;
+  if (of < 0) return true;
+  return f < of || (f == of && b < ob);
 }
 
-__global__ void k_scan(Wave w, int level) {
+__host__ __device__ inline int scan_chunks(int groups) { return groups <= 2 ? 8 : groups <= 4 ? 4 : 2; }
+
+__global__ void __launch_bounds__(1024) k_scan(Wave w, int level) {
   const int j = blockIdx.y;
   const JobState& js = w.js[j];
   if ((int)blockIdx.x >= js.n_pairs) return;
-  const JobParams jp = w.jp[j];
+  const JobParams& jp = w.jp[j];
   const PairRec pr = w.pairs[(size_t)j * w.pair_cap + blockIdx.x];
-  const int G = w.groups;
+  const int G = w.groups, NCH = scan_chunks(G), CB = kBins / NCH;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int c = warp / G, grp = warp % G;
+  const int c = warp / (G * NCH), grp = (warp % (G * NCH)) / NCH, ch = warp % NCH;
   Node* nodes = w.nodes + (size_t)j * kNodeCap;
   TreeNode* tree = w.tree + (size_t)j * kNodeCap;
   const bool live = (level > 0) || (c == 0);
   const int node = level == 0 ? 0 : 2 * pr.parent + 1 + c;
   const bool is_built = (level == 0) || (c == pr.build_right);
   const int built_node = level == 0 ? 0 : 2 * pr.parent + 1 + pr.build_right;
-  const FoldDev fd = w.folds[jp.fold];
+  const FoldDev& fd = w.folds[jp.fold];
   const int f = grp * kLanes + lane;
   const int nc = f < w.f ? fd.ncuts[f] : 0;
   const bool factive = f < w.f && ((js.lmask[f >> 5] >> (f & 31)) & 1u);
@@ -383,43 +447,58 @@ __global__ void k_scan(Wave w, int level) {
   const double inv_sg = js.inv_sg, inv_sh = js.inv_sh;
   float root_gain = nodes[node].root_gain;
   if (level == 0) root_gain = calc_gain(jp, (double)Gt * inv_sg, (double)Ht * inv_sh);
-  Cand best{0.0f, -1, -1, 0, 0};
+  const int b_lo = ch * CB, b_hi = min(b_lo + CB, maxnc);
+
+  __shared__ longlong2 s_sum[32][kLanes];   // chunk sums per warp
+  __shared__ Cand s_c[32];
+  longlong2 acc = make_longlong2(0, 0);
   if (live) {
-    long long GL = 0, HL = 0;
 #pragma unroll 4
-    for (int b = 0; b < maxnc; ++b) {
+    for (int b = b_lo; b < b_hi; ++b) {
       longlong2 e = hbuilt[(size_t)b * kLanes];
       if (!is_built) {
-        longlong2 pe = hpar[(size_t)b * kLanes];
+        const longlong2 pe = hpar[(size_t)b * kLanes];
         e.x = pe.x - e.x; e.y = pe.y - e.y;
         if (write_sib) hown[(size_t)b * kLanes] = e;
       }
+      acc.x += e.x; acc.y += e.y;
+    }
+  }
+  s_sum[warp][lane] = acc;
+  __syncthreads();
+  Cand best{0.0f, -1, -1, 0, 0};
+  if (live && factive) {
+    long long GL = 0, HL = 0;
+    for (int k = 0; k < ch; ++k) { const longlong2 t = s_sum[warp - ch + k][lane]; GL += t.x; HL += t.y; }
+    const int hi = min(b_hi, nc);
+    for (int b = b_lo; b < hi; ++b) {
+      longlong2 e = hbuilt[(size_t)b * kLanes];
+      if (!is_built) { const longlong2 pe = hpar[(size_t)b * kLanes]; e.x = pe.x - e.x; e.y = pe.y - e.y; }
       GL += e.x; HL += e.y;
-      if (factive && b < nc && (e.x != 0 || e.y != 0)) {
-        double gl = (double)GL * inv_sg, hl = (double)HL * inv_sh;
-        double gr = (double)(Gt - GL) * inv_sg, hr = (double)(Ht - HL) * inv_sh;
+      if (e.x != 0 || e.y != 0) {   // an empty bin repeats the previous candidate, which never wins (strict >)
+        const double gl = (double)GL * inv_sg, hl = (double)HL * inv_sh;
+        const double gr = (double)(Gt - GL) * inv_sg, hr = (double)(Ht - HL) * inv_sh;
         if (hl >= jp.mcw && hr >= jp.mcw) {
-          float chg = split_gain(jp, gl, hl, gr, hr) - root_gain;
+          const float chg = split_gain(jp, gl, hl, gr, hr) - root_gain;
           if (!isinf(chg) && chg > best.chg) { best.chg = chg; best.f = f; best.b = b; best.GL = GL; best.HL = HL; }
         }
       }
     }
   }
   for (int d = 16; d; d >>= 1) {
-    float ochg = __shfl_xor_sync(0xffffffffu, best.chg, d);
-    int of = __shfl_xor_sync(0xffffffffu, best.f, d);
-    int ob = __shfl_xor_sync(0xffffffffu, best.b, d);
-    long long oGL = __shfl_xor_sync(0xffffffffu, best.GL, d);
-    long long oHL = __shfl_xor_sync(0xffffffffu, best.HL, d);
-    if (better(ochg, of, best.chg, best.f)) { best.chg = ochg; best.f = of; best.b = ob; best.GL = oGL; best.HL = oHL; }
+    const float ochg = __shfl_xor_sync(0xffffffffu, best.chg, d);
+    const int of = __shfl_xor_sync(0xffffffffu, best.f, d);
+    const int ob = __shfl_xor_sync(0xffffffffu, best.b, d);
+    const long long oGL = __shfl_xor_sync(0xffffffffu, best.GL, d);
+    const long long oHL = __shfl_xor_sync(0xffffffffu, best.HL, d);
+    if (better(ochg, of, ob, best.chg, best.f, best.b)) { best.chg = ochg; best.f = of; best.b = ob; best.GL = oGL; best.HL = oHL; }
   }
-  __shared__ Cand s_c[16];
   if (lane == 0) s_c[warp] = best;
   __syncthreads();
-  if (!(lane == 0 && grp == 0 && live)) return;
-  for (int g2 = 1; g2 < G; ++g2) {
-    const Cand o = s_c[c * G + g2];
-    if (better(o.chg, o.f, best.chg, best.f)) best = o;
+  if (!(lane == 0 && grp == 0 && ch == 0 && live)) return;
+  for (int k = 1; k < G * NCH; ++k) {
+    const Cand o = s_c[warp + k];
+    if (better(o.chg, o.f, o.b, best.chg, best.f, best.b)) best = o;
   }
   Node& nd = nodes[node];
   if (level == 0) {
@@ -428,7 +507,7 @@ __global__ void k_scan(Wave w, int level) {
   }
   bool valid = best.f >= 0 && best.chg > kRtEps;   // CPUExpandEntry::IsValid
   if (valid) {
-    double hl = (double)best.HL * inv_sh, hr = (double)(Ht - best.HL) * inv_sh;
+    const double hl = (double)best.HL * inv_sh, hr = (double)(Ht - best.HL) * inv_sh;
     if (hl == 0.0 || hr == 0.0) valid = false;
     if (best.chg < jp.gamma) valid = false;
   }
@@ -442,42 +521,60 @@ __global__ void k_scan(Wave w, int level) {
   tree[node] = TreeNode{0.f, (int16_t)best.f, (uint8_t)best.b, (uint8_t)kSplit};
   const uint8_t child_state = (level + 1 < jp.max_depth) ? kOpen : kLeaf;   // Driver::IsChildValid
   const long long cg[2] = {best.GL, Gt - best.GL}, chh[2] = {best.HL, Ht - best.HL};
-  for (int s = 0; s < 2; ++s) {
-    Node& ch = nodes[2 * node + 1 + s];
-    double g = (double)cg[s] * inv_sg, h = (double)chh[s] * inv_sh;
-    ch.G = cg[s]; ch.H = chh[s];
-    ch.leaf = jp.eta * calc_weight(jp, g, h);
-    ch.root_gain = calc_gain(jp, g, h);
-    ch.loss_chg = 0.f; ch.feat = -1; ch.bin = 0; ch.state = child_state;
-    ch.begin = 0; ch.cnt = 0; ch.buf = 0;
-    tree[2 * node + 1 + s] = TreeNode{ch.leaf, (int16_t)-1, (uint8_t)0, child_state};
+  for (int sd = 0; sd < 2; ++sd) {
+    Node& chn = nodes[2 * node + 1 + sd];
+    const double g = (double)cg[sd] * inv_sg, h = (double)chh[sd] * inv_sh;
+    chn.G = cg[sd]; chn.H = chh[sd];
+    chn.leaf = jp.eta * calc_weight(jp, g, h);
+    chn.root_gain = calc_gain(jp, g, h);
+    chn.loss_chg = 0.f; chn.feat = -1; chn.bin = 0; chn.state = child_state;
+    chn.begin = 0; chn.cnt = 0; chn.buf = 0;
+    tree[2 * node + 1 + sd] = TreeNode{chn.leaf, (int16_t)-1, (uint8_t)0, child_state};
   }
 }
 
 // ------------------------------------------------------------------ X7: stable row partition
-__global__ void k_plan_part(Wave w, int level) {
-  const int j = blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= w.n_jobs) return;
+__global__ void __launch_bounds__(256) k_plan_part(Wave w, int level) {
+  const int j = blockIdx.x;
   JobState& js = w.js[j];
-  const JobParams jp = w.jp[j];
-  js.n_part_items = 0;
-  if (!js.active || level + 1 >= jp.max_depth) return;
+  const JobParams& jp = w.jp[j];
+  if (!js.active || level + 1 >= jp.max_depth) { if (threadIdx.x == 0) js.n_part_items = 0; return; }
   const Node* nodes = w.nodes + (size_t)j * kNodeCap;
   PartItem* items = w.pitems + (size_t)j * w.part_cap;
-  int ni = 0;
-  const int first = level_first(level), last = level_first(level + 1);
-  for (int nidx = first; nidx < last; ++nidx) {
-    const Node& nd = nodes[nidx];
+  __shared__ int s_scan[256];
+  const int n_lvl = 1 << level, first = level_first(level);
+  int nid[2], chunks[2];
+  for (int s2 = 0; s2 < 2; ++s2) {
+    const int li = 2 * threadIdx.x + s2;
+    nid[s2] = -1; chunks[s2] = 0;
+    if (li >= n_lvl) continue;
+    const Node& nd = nodes[first + li];
     if (nd.state != kSplit) continue;
-    int chunks = (int)((nd.cnt + kPartRows - 1) / kPartRows);
+    nid[s2] = first + li;
+    chunks[s2] = (int)((nd.cnt + kPartRows - 1) / kPartRows);
+  }
+  const int v = chunks[0] + chunks[1];
+  s_scan[threadIdx.x] = v;
+  __syncthreads();
+  for (int d = 1; d < 256; d <<= 1) {
+    const int t = threadIdx.x >= d ? s_scan[threadIdx.x - d] : 0;
+    __syncthreads();
+    s_scan[threadIdx.x] += t;
+    __syncthreads();
+  }
+  int ni = s_scan[threadIdx.x] - v;
+  for (int s2 = 0; s2 < 2; ++s2) {
+    if (nid[s2] < 0) continue;
+    const Node& nd = nodes[nid[s2]];
     const int first_item = ni;
-    for (int c = 0; c < chunks && ni < w.part_cap; ++c) {
-      uint32_t b = (uint32_t)c * kPartRows;
-      uint32_t cnt = nd.cnt - b < (uint32_t)kPartRows ? nd.cnt - b : (uint32_t)kPartRows;
-      items[ni++] = PartItem{nidx, nd.begin + b, cnt, first_item, chunks, nd.begin, nd.cnt, (int)nd.buf};
+    for (int c = 0; c < chunks[s2]; ++c, ++ni) {
+      if (ni >= w.part_cap) break;
+      const uint32_t b = (uint32_t)c * kPartRows;
+      const uint32_t cnt = nd.cnt - b < (uint32_t)kPartRows ? nd.cnt - b : (uint32_t)kPartRows;
+      items[ni] = PartItem{nid[s2], nd.begin + b, cnt, first_item, chunks[s2], nd.begin, nd.cnt, (int)nd.buf};
     }
   }
-  js.n_part_items = ni;
+  if (threadIdx.x == 255) js.n_part_items = min(s_scan[255], w.part_cap);
 }
 
 __global__ void __launch_bounds__(256) k_part_count(Wave w, int level) {
@@ -731,9 +828,9 @@ void launch_hist(const Wave& w, int level, cudaStream_t s) {
 }
 void launch_scan(const Wave& w, int level, cudaStream_t s) {
   int pairs = level == 0 ? 1 : (1 << (level - 1));
-  k_scan<<<dim3(pairs, w.n_jobs), 2 * w.groups * 32, 0, s>>>(w, level);
+  k_scan<<<dim3(pairs, w.n_jobs), 2 * w.groups * scan_chunks(w.groups) * 32, 0, s>>>(w, level);
 }
-void launch_plan_part(const Wave& w, int level, cudaStream_t s) { k_plan_part<<<(w.n_jobs + 63) / 64, 64, 0, s>>>(w, level); }
+void launch_plan_part(const Wave& w, int level, cudaStream_t s) { k_plan_part<<<w.n_jobs, 256, 0, s>>>(w, level); }
 void launch_part_count(const Wave& w, int level, cudaStream_t s) {
   k_part_count<<<dim3(part_items_bound(w, level), w.n_jobs), 256, 0, s>>>(w, level);
 }
