@@ -43,6 +43,7 @@ def parse_args():
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--cpu-rounds", type=int, default=2, help="boosting rounds in the CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--rounds", type=int, default=0, help="override boosting rounds (profiling only; not a bench line)")
     return ap.parse_args()
 
 
@@ -184,6 +185,10 @@ def run_reference(args):
 
 def main():
     args = parse_args()
+    if args.rounds:
+        wl = list(WORKLOADS[args.workload]); wl[3] = args.rounds
+        WORKLOADS[args.workload + "-profile"] = tuple(wl)
+        args.workload = args.workload + "-profile"
     if args.impl == "reference":
         return run_reference(args)
     import torch

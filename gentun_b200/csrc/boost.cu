@@ -79,7 +79,7 @@ __device__ void prepare_next_round(const Wave& w, int j) {
   int e;
   float sg = 1.0f, sh = 1.0f;
   if (gmax > 0.f && isfinite(gmax)) { frexpf(gmax, &e); sg = ldexpf(1.0f, kQuantBits - e); }
-  if (hmax > 0.f && isfinite(hmax)) { frexpf(hmax, &e); sh = ldexpf(1.0f, kQuantBits - e); }
+  if (hmax > 0.f && isfinite(hmax)) { frexpf(hmax, &e); sh = ldexpf(1.0f, kQuantBitsH - e); }
   js.sg = sg; js.sh = sh;
   js.inv_sg = 1.0 / (double)sg; js.inv_sh = 1.0 / (double)sh;
   js.gmax_bits = 0u; js.hmax_bits = 0u;
@@ -224,10 +224,10 @@ __global__ void __launch_bounds__(256) k_plan_hist(Wave w, int level) {
   // each thread owns up to two parents (2 * 256 >= 2^(kMaxDepth - 1))
   const int n_par = level == 0 ? 1 : (1 << (level - 1));
   const int first = level == 0 ? 0 : level_first(level - 1);
-  int bnode[2], chunks[2];
+  int bnode[2], chunks[2], shr[2];
   for (int s2 = 0; s2 < 2; ++s2) {
     const int pi = 2 * threadIdx.x + s2;
-    bnode[s2] = -1; chunks[s2] = 0;
+    bnode[s2] = -1; chunks[s2] = 0; shr[s2] = 0;
     if (pi >= n_par) continue;
     if (level == 0) {
       bnode[s2] = 0;
@@ -240,9 +240,11 @@ __global__ void __launch_bounds__(256) k_plan_hist(Wave w, int level) {
     const uint32_t cnt = nodes[bnode[s2]].cnt;
     chunks[s2] = (int)((cnt + kHistRows - 1) / kHistRows);
     if (chunks[s2] < 1) chunks[s2] = 1;
+    // several CTAs, or one CTA that may flush mid-item: accumulate with atomics into a cleared histogram
+    shr[s2] = chunks[s2] > 1 || cnt > (uint32_t)kEpochRows;
   }
   __syncthreads();   // s_rows initialised
-  int v[3] = {chunks[0] + chunks[1], (bnode[0] >= 0) + (bnode[1] >= 0), (chunks[0] > 1) + (chunks[1] > 1)};
+  int v[3] = {chunks[0] + chunks[1], (bnode[0] >= 0) + (bnode[1] >= 0), shr[0] + shr[1]};
   for (int q = 0; q < 3; ++q) s_scan[q][threadIdx.x] = v[q];
   __syncthreads();
   for (int d = 1; d < 256; d <<= 1) {   // Hillis-Steele inclusive scan of the three counters
@@ -261,9 +263,9 @@ __global__ void __launch_bounds__(256) k_plan_hist(Wave w, int level) {
       if (ni >= w.hist_cap) break;
       const uint32_t b = (uint32_t)c * kHistRows;
       const uint32_t cnt = bn.cnt > b ? (bn.cnt - b < (uint32_t)kHistRows ? bn.cnt - b : (uint32_t)kHistRows) : 0u;
-      items[ni] = HistItem{bnode[s2], bn.begin + b, cnt, (chunks[s2] > 1 ? 1 : 0) | ((int)bn.buf << 1)};
+      items[ni] = HistItem{bnode[s2], bn.begin + b, cnt, shr[s2] | ((int)bn.buf << 1)};
     }
-    if (chunks[s2] > 1) { if (nz < w.hist_cap) zl[nz] = bnode[s2]; ++nz; }
+    if (shr[s2]) { if (nz < w.hist_cap) zl[nz] = bnode[s2]; ++nz; }
     if (np < w.pair_cap) pairs[np] = level == 0 ? PairRec{-1, 0} : PairRec{(bnode[s2] - 1) >> 1, (bnode[s2] & 1) ? 0 : 1};
     ++np;
     rows_mine += bn.cnt;
@@ -306,28 +308,37 @@ __device__ __forceinline__ uint4 ld_stream(const uint4* p) {
   return r;
 }
 
-struct HistStage { uint4 b0, b1; int2 g0, g1; };
+// UNITS = 16-byte units of a row handled by one CTA: 2 = one feature group (32 B of the row, 64 KiB of
+// shared histogram, 3 CTAs/SM), 4 = a pair of groups (the whole 64-byte line of the row, 128 KiB, 1 CTA/SM).
+template <int UNITS>
+struct HistStage { uint4 b[UNITS]; int2 g[UNITS]; };
 
-// 32 rows of a warp's stripe: two sub-batches of 16 rows, lane = (row slot rl, 16-byte half)
-__device__ __forceinline__ void hist_load(HistStage& st, uint32_t myrow, int rl, const uint8_t* __restrict__ bins_half,
-                                          const int2* __restrict__ gq, int fpad) {
-  const uint32_t r0 = __shfl_sync(0xffffffffu, myrow, rl), r1 = __shfl_sync(0xffffffffu, myrow, 16 + rl);
-  // rows past the end of the item read row 0 and add a zero gradient: no predicate in the hot loop
-  const bool v0 = r0 != 0xffffffffu, v1 = r1 != 0xffffffffu;
-  const uint32_t a0 = v0 ? r0 : 0u, a1 = v1 ? r1 : 0u;
-  st.b0 = ld_stream(reinterpret_cast<const uint4*>(bins_half + (size_t)a0 * fpad));
-  st.b1 = ld_stream(reinterpret_cast<const uint4*>(bins_half + (size_t)a1 * fpad));
-  const int2 z = make_int2(0, 0);
-  st.g0 = v0 ? gq[a0] : z;
-  st.g1 = v1 ? gq[a1] : z;
+__device__ __forceinline__ void red_shared(uint32_t addr, int v) {
+  asm volatile("red.shared.add.s32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ void red_shared_hi(uint32_t addr, int v) {   // hessian plane sits 32 KiB above
+  asm volatile("red.shared.add.s32 [%0+32768], %1;" ::"r"(addr), "r"(v) : "memory");
 }
 
-__device__ __forceinline__ void hist_accumulate(const uint4 v, const int2 g2, int q, int rb, const int (&cs)[16], char* shb) {
-  // rotate the 16 bytes right by rl bytes: word rotation by q = rl / 4, then funnel shift by rb bits
-  const uint32_t u0 = q == 0 ? v.x : q == 1 ? v.y : q == 2 ? v.z : v.w;
-  const uint32_t u1 = q == 0 ? v.y : q == 1 ? v.z : q == 2 ? v.w : v.x;
-  const uint32_t u2 = q == 0 ? v.z : q == 1 ? v.w : q == 2 ? v.x : v.y;
-  const uint32_t u3 = q == 0 ? v.w : q == 1 ? v.x : q == 2 ? v.y : v.z;
+// 32 rows of a warp's stripe = UNITS sub-batches of 32/UNITS rows; lane = (row slot, 16-byte unit)
+template <int UNITS>
+__device__ __forceinline__ void hist_load(HistStage<UNITS>& st, uint32_t myrow, int rslot, const uint8_t* __restrict__ bins_unit,
+                                          const int2* __restrict__ gq, int fpad) {
+#pragma unroll
+  for (int sb = 0; sb < UNITS; ++sb) {
+    const uint32_t r = __shfl_sync(0xffffffffu, myrow, sb * (32 / UNITS) + rslot);
+    // rows past the end of the item read row 0 and add a zero gradient: no predicate in the hot loop
+    const bool ok = r != 0xffffffffu;
+    const uint32_t a = ok ? r : 0u;
+    st.b[sb] = ld_stream(reinterpret_cast<const uint4*>(bins_unit + (size_t)a * fpad));
+    st.g[sb] = ok ? gq[a] : make_int2(0, 0);
+  }
+}
+
+__device__ __forceinline__ void hist_accumulate(const uint4 v, const int2 g2, bool q1, bool q2, int rb, const uint32_t (&cs)[16]) {
+  // rotate the 16 bytes right by `rot` bytes: two conditional word rotations, then a funnel shift
+  const uint32_t a0 = q1 ? v.y : v.x, a1 = q1 ? v.z : v.y, a2 = q1 ? v.w : v.z, a3 = q1 ? v.x : v.w;
+  const uint32_t u0 = q2 ? a2 : a0, u1 = q2 ? a3 : a1, u2 = q2 ? a0 : a2, u3 = q2 ? a1 : a3;
   uint32_t r[4];
   r[0] = __funnelshift_r(u0, u1, rb);
   r[1] = __funnelshift_r(u1, u2, rb);
@@ -336,67 +347,111 @@ __device__ __forceinline__ void hist_accumulate(const uint4 v, const int2 g2, in
 #pragma unroll
   for (int s = 0; s < 16; ++s) {
     const uint32_t bin = __byte_perm(r[s >> 2], 0u, 0x4440u + (uint32_t)(s & 3));
-    char* cell = shb + (bin * (kLanes * 4u) + (uint32_t)cs[s]);
-    atomicAdd(reinterpret_cast<int*>(cell), g2.x);
-    atomicAdd(reinterpret_cast<int*>(cell + kBins * kLanes * 4), g2.y);
+    const uint32_t cell = bin * (kLanes * 4u) + cs[s];
+    red_shared(cell, g2.x);
+    red_shared_hi(cell, g2.y);
   }
 }
 
-__global__ void __launch_bounds__(kHistThreads, 3) k_hist(Wave w, int level) {
+// Shared partial sums are int32.  A cell can never exceed the sum of |q| over the rows the CTA has
+// accumulated since its last flush, so the CTA tracks that sum (and the hessian sum) and flushes to
+// the int64 global histogram before another epoch of kEpochRows rows could overflow.
+template <int UNITS>
+__device__ __forceinline__ void hist_flush(const Wave& w, const JobParams& jp, int level, const HistItem& it, int cg, int* sh,
+                                           bool atomic, bool rezero) {
+  constexpr int kThreads = UNITS == 2 ? 256 : 512;
+  constexpr int kGroupsPerCta = UNITS / 2;
+  HistEntry* dst = node_hist(w, jp, level, it.node) + (size_t)cg * kGroupsPerCta * (kBins * kLanes);
+  for (int i = threadIdx.x; i < kGroupsPerCta * kBins * kLanes; i += kThreads) {
+    const int gsel = i / (kBins * kLanes), cell = i % (kBins * kLanes);
+    int* pg = sh + gsel * (2 * kBins * kLanes) + cell;
+    const int g = pg[0], h = pg[kBins * kLanes];
+    if (atomic) {
+      if (g) atomicAdd(reinterpret_cast<unsigned long long*>(&dst[i].g), (unsigned long long)(long long)g);
+      if (h) atomicAdd(reinterpret_cast<unsigned long long*>(&dst[i].h), (unsigned long long)(long long)h);
+    } else {
+      reinterpret_cast<longlong2*>(dst)[i] = make_longlong2((long long)g, (long long)h);
+    }
+    if (rezero) { pg[0] = 0; pg[kBins * kLanes] = 0; }
+  }
+}
+
+template <int UNITS>
+__global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 3 : 1) k_hist(Wave w, int level) {
+  constexpr int kThreads = UNITS == 2 ? 256 : 512;
+  constexpr int kGroupsPerCta = UNITS / 2;
+  constexpr uint32_t kStride = (kThreads / 32) * 32u;          // rows per CTA iteration
+  constexpr int kEpochIters = kEpochRows / (int)kStride;       // CTA iterations between overflow checks
   const int j = blockIdx.y;
   const JobState& js = w.js[j];
-  const int item_idx = blockIdx.x / w.groups, grp = blockIdx.x % w.groups;
+  const int ncg = w.groups / kGroupsPerCta;
+  const int item_idx = blockIdx.x / ncg, cg = blockIdx.x % ncg;
   if (item_idx >= js.n_hist_items) return;
   const JobParams& jp = w.jp[j];
   const HistItem it = w.hitems[(size_t)j * w.hist_cap + item_idx];
-  extern __shared__ int sh[];
-  int* sh_g = sh;
-  int* sh_h = sh + kBins * kLanes;
-  for (int i = threadIdx.x; i < 2 * kBins * kLanes / 4; i += kHistThreads) reinterpret_cast<int4*>(sh)[i] = make_int4(0, 0, 0, 0);
+  extern __shared__ int sh[];   // [group in CTA][g plane | h plane][bin][feature lane]
+  __shared__ unsigned s_abs[2];  // sum |g_q| and sum h_q since the last flush, in units of 64
+  for (int i = threadIdx.x; i < kGroupsPerCta * 2 * kBins * kLanes / 4; i += kThreads) reinterpret_cast<int4*>(sh)[i] = make_int4(0, 0, 0, 0);
+  if (threadIdx.x < 2) s_abs[threadIdx.x] = 0u;
   __syncthreads();
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  const int rl = lane >> 1, half = lane & 1;
-  const int q = rl >> 2, rb = (rl & 3) * 8;
-  const uint8_t* bins_half = w.folds[jp.fold].bins + (size_t)grp * kLanes + half * 16;
+  const int rslot = lane / UNITS, unit = lane % UNITS;
+  const int rot = UNITS == 2 ? rslot : rslot * 2 + (unit >> 1);   // 16 distinct rotations per bank half
+  const bool q1 = (rot >> 2) & 1, q2 = (rot >> 3) & 1;
+  const int rb = (rot & 3) * 8;
+  const uint8_t* bins_unit = w.folds[jp.fold].bins + (size_t)cg * kGroupsPerCta * kLanes + unit * 16;
   const uint32_t* ridx = w.ridx + ((size_t)j * 2 + (size_t)((it.flags >> 1) & 1)) * w.nt_stride + it.begin;
   const int2* gq = w.gq + (size_t)j * w.nt_stride;
   const int fpad = w.fpad;
-  int cs[16];   // byte offset of this lane's feature column at unrolled step s
+  const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(sh);
+  uint32_t cs[16];   // shared address of this lane's feature column (bin 0, g plane) at unrolled step s
 #pragma unroll
-  for (int s = 0; s < 16; ++s) cs[s] = (half * 16 + ((s + rl) & 15)) * 4;
-  char* shb = reinterpret_cast<char*>(sh);
-  constexpr uint32_t kStride = (kHistThreads / 32) * 32u;
-  uint32_t base = (uint32_t)wid * 32u;
-  if (base < it.cnt) {
-    HistStage cur, nxt;
-    uint32_t myrow = base + lane < it.cnt ? ridx[base + lane] : 0xffffffffu;
-    hist_load(cur, myrow, rl, bins_half, gq, fpad);
-    for (;;) {
-      const uint32_t nb = base + kStride;
-      const bool more = nb < it.cnt;
-      if (more) {
-        myrow = nb + lane < it.cnt ? ridx[nb + lane] : 0xffffffffu;
-        hist_load(nxt, myrow, rl, bins_half, gq, fpad);
+  for (int s = 0; s < 16; ++s) {
+    const uint32_t fl = (uint32_t)((unit & 1) * 16 + ((s + rot) & 15));
+    const uint32_t v = sbase + (uint32_t)(unit >> 1) * (2u * kBins * kLanes * 4u) + fl * 4u;
+    asm volatile("mov.u32 %0, %1;" : "=r"(cs[s]) : "r"(v));   // opaque: keep it in a register, never rematerialise
+  }
+  const bool atomic_flush = it.flags & 1;
+  const uint32_t cnt = it.cnt;
+  // three-deep software pipeline: row ids two iterations ahead, bin bytes + gradients one ahead
+  const uint32_t my0 = (uint32_t)wid * 32u + (uint32_t)lane;
+  uint32_t row_b = my0 < cnt ? ridx[my0] : 0xffffffffu;                              // iteration 0
+  uint32_t row_c = my0 + kStride < cnt ? ridx[my0 + kStride] : 0xffffffffu;          // iteration 1
+  HistStage<UNITS> cur, nxt;
+  hist_load<UNITS>(cur, row_b, rslot, bins_unit, gq, fpad);
+  row_b = row_c;
+  const uint32_t n_iter = (cnt + kStride - 1) / kStride;   // CTA-uniform trip count
+  unsigned acc_g = 0u, acc_h = 0u;
+  for (uint32_t itn = 0; itn < n_iter; ++itn) {
+    const uint32_t p2 = my0 + (itn + 2) * kStride;
+    row_c = p2 < cnt ? ridx[p2] : 0xffffffffu;
+    if (itn + 1 < n_iter) hist_load<UNITS>(nxt, row_b, rslot, bins_unit, gq, fpad);
+#pragma unroll
+    for (int sb = 0; sb < UNITS; ++sb) {
+      hist_accumulate(cur.b[sb], cur.g[sb], q1, q2, rb, cs);
+      if (unit == 0) { acc_g += (unsigned)abs(cur.g[sb].x); acc_h += (unsigned)cur.g[sb].y; }   // one lane per row
+    }
+    cur = nxt;
+    row_b = row_c;
+    if ((itn + 1) % kEpochIters == 0 && itn + 1 < n_iter) {
+      // epoch boundary: will another epoch of worst-case rows still fit in int32?
+      const unsigned tg = __reduce_add_sync(0xffffffffu, acc_g >> 3), th = __reduce_add_sync(0xffffffffu, acc_h >> 3);
+      if (lane == 0) { atomicAdd(&s_abs[0], (tg >> 3) + 5u); atomicAdd(&s_abs[1], (th >> 3) + 5u); }   // +5: rounding slack
+      acc_g = 0u; acc_h = 0u;
+      __syncthreads();
+      // s_abs is an upper bound, in units of 64, of sum |g_q| (sum h_q) accumulated since the last flush
+      const unsigned lim = (0x7fffffffu >> 6) - (((unsigned)kEpochRows << kQuantBits) >> 6) - 64u;
+      const bool must = s_abs[0] >= lim || s_abs[1] >= lim;
+      __syncthreads();
+      if (must) {
+        hist_flush<UNITS>(w, jp, level, it, cg, sh, true, true);
+        if (threadIdx.x < 2) s_abs[threadIdx.x] = 0u;
+        __syncthreads();
       }
-      hist_accumulate(cur.b0, cur.g0, q, rb, cs, shb);
-      hist_accumulate(cur.b1, cur.g1, q, rb, cs, shb);
-      if (!more) break;
-      cur = nxt;
-      base = nb;
     }
   }
   __syncthreads();
-  HistEntry* dst = node_hist(w, jp, level, it.node) + (size_t)grp * (kBins * kLanes);
-  if (it.flags & 1) {
-    for (int i = threadIdx.x; i < kBins * kLanes; i += kHistThreads) {
-      int g = sh_g[i], h = sh_h[i];
-      if (g) atomicAdd(reinterpret_cast<unsigned long long*>(&dst[i].g), (unsigned long long)(long long)g);
-      if (h) atomicAdd(reinterpret_cast<unsigned long long*>(&dst[i].h), (unsigned long long)(long long)h);
-    }
-  } else {
-    for (int i = threadIdx.x; i < kBins * kLanes; i += kHistThreads)
-      reinterpret_cast<longlong2*>(dst)[i] = make_longlong2((long long)sh_g[i], (long long)sh_h[i]);
-  }
+  hist_flush<UNITS>(w, jp, level, it, cg, sh, atomic_flush, false);
 }
 
 // ------------------------------------------------------------------ X6: split enumeration
@@ -810,7 +865,9 @@ __global__ void k_dump_node_rows(Wave w, gt_node_rows* out) {
 int hist_smem_bytes() { return kHistSmem; }
 
 int configure_kernels() {
-  return (int)cudaFuncSetAttribute(k_hist, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmem);
+  cudaError_t e = cudaFuncSetAttribute(k_hist<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmem);
+  if (e != cudaSuccess) return (int)e;
+  return (int)cudaFuncSetAttribute(k_hist<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * kHistSmem);
 }
 
 void launch_init_wave(const Wave& w, cudaStream_t s) {
@@ -824,7 +881,8 @@ void launch_plan_hist(const Wave& w, int level, cudaStream_t s) { k_plan_hist<<<
 void launch_hist_zero(const Wave& w, int level, cudaStream_t s) { k_hist_zero<<<dim3(32, w.n_jobs), 256, 0, s>>>(w, level); }
 void launch_hist(const Wave& w, int level, cudaStream_t s) {
   int cap = hist_items_bound(w, level);
-  k_hist<<<dim3(cap * w.groups, w.n_jobs), kHistThreads, kHistSmem, s>>>(w, level);
+  if (w.groups % 2 == 0) k_hist<4><<<dim3(cap * (w.groups / 2), w.n_jobs), 512, 2 * kHistSmem, s>>>(w, level);
+  else k_hist<2><<<dim3(cap * w.groups, w.n_jobs), 256, kHistSmem, s>>>(w, level);
 }
 void launch_scan(const Wave& w, int level, cudaStream_t s) {
   int pairs = level == 0 ? 1 : (1 << (level - 1));

@@ -9,9 +9,11 @@ constexpr int kBins = 256;          // max_bin (xgboost default, never overridde
 constexpr int kLanes = 32;          // features per histogram group == smem banks
 constexpr int kMaxDepth = 10;       // max_depth gene range 3..10 (gentun/individuals.py:167)
 constexpr int kNodeCap = 2048;      // heap slots per tree (2^(10+1)-1 used)
-constexpr int kHistRows = 2048;     // rows per histogram work item (bounds int32 partial sums)
+constexpr int kHistRows = 16384;    // rows per histogram work item
+constexpr int kEpochRows = 2048;    // rows between int32-overflow checks of the shared partial sums
 constexpr int kPartRows = 2048;     // rows per partition work item
-constexpr int kQuantBits = 19;      // |quantised gradient| <= 2^19  (2^19 * 2048 = 2^30 < 2^31)
+constexpr int kQuantBits = 19;      // |quantised gradient|, quantised hessian <= 2^19 (one epoch adds < 2^30)
+constexpr int kQuantBitsH = 17;     // hessians are near-constant (1 for squared error): fewer bits, fewer flushes
 constexpr int kPredRows = 2048;     // rows per predict CTA
 constexpr int kMaskWords = 8;       // feature masks: up to 256 features
 
