@@ -285,6 +285,18 @@ __device__ __forceinline__ HistEntry* node_hist(const Wave& w, const JobParams& 
   return w.hist + ((level & 1) ? jp.hist_off[1] : jp.hist_off[0]) + (size_t)(node - level_first(level)) * w.groups * (kBins * kLanes);
 }
 
+// A node with at most kEpochRows rows keeps its histogram as int32 pairs (|cell| <= rows * 2^19 < 2^31):
+// half the bytes for the deep levels, where histogram traffic dominates.  Larger nodes use int64 pairs.
+__device__ __forceinline__ bool node_narrow(uint32_t cnt) { return cnt <= (uint32_t)kEpochRows; }
+__device__ __forceinline__ longlong2 load_cell(const HistEntry* slot, bool narrow, size_t idx) {
+  if (narrow) { const int2 v = reinterpret_cast<const int2*>(slot)[idx]; return make_longlong2((long long)v.x, (long long)v.y); }
+  return reinterpret_cast<const longlong2*>(slot)[idx];
+}
+__device__ __forceinline__ void store_cell(HistEntry* slot, bool narrow, size_t idx, const longlong2 e) {
+  if (narrow) reinterpret_cast<int2*>(slot)[idx] = make_int2((int)e.x, (int)e.y);
+  else reinterpret_cast<longlong2*>(slot)[idx] = e;
+}
+
 __global__ void __launch_bounds__(256) k_hist_zero(Wave w, int level) {
   const int j = blockIdx.y;
   const JobState& js = w.js[j];
@@ -370,7 +382,7 @@ __device__ __forceinline__ void hist_flush(const Wave& w, const JobParams& jp, i
       if (g) atomicAdd(reinterpret_cast<unsigned long long*>(&dst[i].g), (unsigned long long)(long long)g);
       if (h) atomicAdd(reinterpret_cast<unsigned long long*>(&dst[i].h), (unsigned long long)(long long)h);
     } else {
-      reinterpret_cast<longlong2*>(dst)[i] = make_longlong2((long long)g, (long long)h);
+      reinterpret_cast<int2*>(dst)[i] = make_int2(g, h);   // single-CTA node (<= kEpochRows rows): narrow format
     }
     if (rezero) { pg[0] = 0; pg[kBins * kLanes] = 0; }
   }
@@ -495,9 +507,11 @@ __global__ void __launch_bounds__(1024) k_scan(Wave w, int level) {
   const int maxnc = w.grp_maxnc[jp.fold * G + grp];
   const bool write_sib = live && !is_built && (level + 1 < jp.max_depth);
   const size_t goff = (size_t)grp * (kBins * kLanes) + lane;
-  const longlong2* hbuilt = reinterpret_cast<const longlong2*>(node_hist(w, jp, level, built_node)) + goff;
-  const longlong2* hpar = level > 0 ? reinterpret_cast<const longlong2*>(node_hist(w, jp, level - 1, pr.parent)) + goff : nullptr;
-  longlong2* hown = reinterpret_cast<longlong2*>(node_hist(w, jp, level, node)) + goff;
+  const HistEntry* hbuilt = node_hist(w, jp, level, built_node);
+  const HistEntry* hpar = level > 0 ? node_hist(w, jp, level - 1, pr.parent) : nullptr;
+  HistEntry* hown = node_hist(w, jp, level, node);
+  const bool nar_b = node_narrow(nodes[built_node].cnt), nar_o = node_narrow(nodes[node].cnt);
+  const bool nar_p = level > 0 ? node_narrow(nodes[pr.parent].cnt) : false;
   const long long Gt = nodes[node].G, Ht = nodes[node].H;
   const double inv_sg = js.inv_sg, inv_sh = js.inv_sh;
   float root_gain = nodes[node].root_gain;
@@ -510,11 +524,11 @@ __global__ void __launch_bounds__(1024) k_scan(Wave w, int level) {
   if (live) {
 #pragma unroll 4
     for (int b = b_lo; b < b_hi; ++b) {
-      longlong2 e = hbuilt[(size_t)b * kLanes];
+      longlong2 e = load_cell(hbuilt, nar_b, goff + (size_t)b * kLanes);
       if (!is_built) {
-        const longlong2 pe = hpar[(size_t)b * kLanes];
+        const longlong2 pe = load_cell(hpar, nar_p, goff + (size_t)b * kLanes);
         e.x = pe.x - e.x; e.y = pe.y - e.y;
-        if (write_sib) hown[(size_t)b * kLanes] = e;
+        if (write_sib) store_cell(hown, nar_o, goff + (size_t)b * kLanes, e);
       }
       acc.x += e.x; acc.y += e.y;
     }
@@ -527,8 +541,8 @@ __global__ void __launch_bounds__(1024) k_scan(Wave w, int level) {
     for (int k = 0; k < ch; ++k) { const longlong2 t = s_sum[warp - ch + k][lane]; GL += t.x; HL += t.y; }
     const int hi = min(b_hi, nc);
     for (int b = b_lo; b < hi; ++b) {
-      longlong2 e = hbuilt[(size_t)b * kLanes];
-      if (!is_built) { const longlong2 pe = hpar[(size_t)b * kLanes]; e.x = pe.x - e.x; e.y = pe.y - e.y; }
+      longlong2 e = load_cell(hbuilt, nar_b, goff + (size_t)b * kLanes);
+      if (!is_built) { const longlong2 pe = load_cell(hpar, nar_p, goff + (size_t)b * kLanes); e.x = pe.x - e.x; e.y = pe.y - e.y; }
       GL += e.x; HL += e.y;
       if (e.x != 0 || e.y != 0) {   // an empty bin repeats the previous candidate, which never wins (strict >)
         const double gl = (double)GL * inv_sg, hl = (double)HL * inv_sh;
@@ -632,26 +646,26 @@ __global__ void __launch_bounds__(256) k_plan_part(Wave w, int level) {
   if (threadIdx.x == 255) js.n_part_items = min(s_scan[255], w.part_cap);
 }
 
+// The split feature's bin of a row comes from the feature-major copy of the bin matrix: rows of a node
+// are ascending, so neighbouring rows share DRAM lines (1 useful byte per 64-byte line otherwise).
 __global__ void __launch_bounds__(256) k_part_count(Wave w, int level) {
   const int j = blockIdx.y;
   const JobState& js = w.js[j];
   if ((int)blockIdx.x >= js.n_part_items) return;
-  const JobParams jp = w.jp[j];
+  const JobParams& jp = w.jp[j];
   const PartItem it = w.pitems[(size_t)j * w.part_cap + blockIdx.x];
   const Node& nd = w.nodes[(size_t)j * kNodeCap + it.node];
-  const int feat = nd.feat; const uint32_t sbin = nd.bin;
-  const uint8_t* bins = w.folds[jp.fold].bins + feat;
+  const uint32_t sbin = nd.bin;
+  const uint8_t* col = w.folds[jp.fold].bins_col + (size_t)nd.feat * (size_t)w.n;
   const uint32_t* src = w.ridx + ((size_t)j * 2 + it.buf) * w.nt_stride + it.begin;
-  uint32_t* bits = w.pbits + ((size_t)j * w.part_cap + blockIdx.x) * (kPartRows / 32);
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   int cnt = 0;
 #pragma unroll
   for (int t = 0; t < kPartRows / 256; ++t) {
     const uint32_t p = (uint32_t)t * 256u + threadIdx.x;
     bool left = false;
-    if (p < it.cnt) { uint32_t row = src[p]; left = (uint32_t)bins[(size_t)row * w.fpad] <= sbin; }
-    uint32_t m = __ballot_sync(0xffffffffu, left);
-    if (lane == 0) { bits[t * 8 + wid] = m; cnt += __popc(m); }
+    if (p < it.cnt) left = (uint32_t)col[src[p]] <= sbin;
+    cnt += __popc(__ballot_sync(0xffffffffu, left));
   }
   __shared__ int s_cnt[8];
   if (lane == 0) s_cnt[wid] = cnt;
@@ -667,46 +681,60 @@ __global__ void __launch_bounds__(256) k_part_scatter(Wave w, int level) {
   const int j = blockIdx.y;
   const JobState& js = w.js[j];
   if ((int)blockIdx.x >= js.n_part_items) return;
+  const JobParams& jp = w.jp[j];
   const PartItem it = w.pitems[(size_t)j * w.part_cap + blockIdx.x];
+  const Node& nd = w.nodes[(size_t)j * kNodeCap + it.node];
+  const uint32_t sbin = nd.bin;
+  const uint8_t* col = w.folds[jp.fold].bins_col + (size_t)nd.feat * (size_t)w.n;
   const int* pleft = w.pleft + (size_t)j * w.part_cap;
-  const uint32_t* bits = w.pbits + ((size_t)j * w.part_cap + blockIdx.x) * (kPartRows / 32);
-  const uint32_t* src = w.ridx + ((size_t)j * 2 + it.buf) * w.nt_stride;
+  const uint32_t* src = w.ridx + ((size_t)j * 2 + it.buf) * w.nt_stride + it.begin;
   uint32_t* dst = w.ridx + ((size_t)j * 2 + (it.buf ^ 1)) * w.nt_stride;
-  __shared__ int s_pref[kPartRows / 32];
+  constexpr int kIters = kPartRows / 256;
+  __shared__ int s_pref[kIters * 8];
   __shared__ int s_red[2][8];
   __shared__ int s_prev, s_total;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   int prevL = 0, totL = 0;
   for (int i = it.first_item + threadIdx.x; i < it.first_item + it.n_items; i += blockDim.x) {
-    int v = pleft[i];
+    const int v = pleft[i];
     totL += v;
     if (i < (int)blockIdx.x) prevL += v;
   }
   for (int d = 16; d; d >>= 1) { prevL += __shfl_xor_sync(0xffffffffu, prevL, d); totL += __shfl_xor_sync(0xffffffffu, totL, d); }
   if (lane == 0) { s_red[0][wid] = prevL; s_red[1][wid] = totL; }
+  uint32_t rows[kIters];
+  uint32_t words[kIters];
+#pragma unroll
+  for (int t = 0; t < kIters; ++t) {
+    const uint32_t p = (uint32_t)t * 256u + threadIdx.x;
+    bool left = false;
+    rows[t] = 0u;
+    if (p < it.cnt) { rows[t] = src[p]; left = (uint32_t)col[rows[t]] <= sbin; }
+    words[t] = __ballot_sync(0xffffffffu, left);
+    if (lane == 0) s_pref[t * 8 + wid] = __popc(words[t]);
+  }
   __syncthreads();
   if (threadIdx.x == 0) {
     int a = 0, b = 0;
     for (int q2 = 0; q2 < 8; ++q2) { a += s_red[0][q2]; b += s_red[1][q2]; }
     s_prev = a; s_total = b;
     int run = 0;
-    for (int q2 = 0; q2 < kPartRows / 32; ++q2) { s_pref[q2] = run; run += __popc(bits[q2]); }
+    for (int q2 = 0; q2 < kIters * 8; ++q2) { const int c = s_pref[q2]; s_pref[q2] = run; run += c; }
   }
   __syncthreads();
   prevL = s_prev; totL = s_total;
   const uint32_t rel0 = it.begin - it.node_begin;
 #pragma unroll
-  for (int t = 0; t < kPartRows / 256; ++t) {
+  for (int t = 0; t < kIters; ++t) {
     const uint32_t p = (uint32_t)t * 256u + threadIdx.x;
     if (p < it.cnt) {
-      const uint32_t word = bits[t * 8 + wid];
-      const uint32_t row = src[it.begin + p];
+      const uint32_t word = words[t];
       const int lrank = s_pref[t * 8 + wid] + __popc(word & ((1u << lane) - 1u));
       const bool left = (word >> lane) & 1u;
       const uint32_t rel = rel0 + p;
       const uint32_t d = left ? it.node_begin + (uint32_t)(prevL + lrank)
                               : it.node_begin + (uint32_t)totL + (rel - (uint32_t)(prevL + lrank));
-      dst[d] = row;
+      dst[d] = rows[t];
     }
   }
   if ((int)blockIdx.x == it.first_item && threadIdx.x == 0) {

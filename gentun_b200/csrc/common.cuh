@@ -79,6 +79,7 @@ struct IndState {
 
 struct FoldDev {
   const uint8_t* bins;   // [n][fpad] fold order (train slice rows then test slice rows)
+  const uint8_t* bins_col;  // [f][n] feature-major copy, read by the partition kernels
   const float* y;        // [n] fold order
   const float* cuts;     // [f][256]
   const int* ncuts;      // [f]
@@ -108,7 +109,6 @@ struct Wave {            // passed by value to kernels
   int* zlist;            // [n_jobs][hist_cap] nodes whose histogram must be cleared
   PairRec* pairs;        // [n_jobs][pair_cap]
   PartItem* pitems;      // [n_jobs][part_cap]
-  uint32_t* pbits;       // [n_jobs][part_cap][kPartRows/32]
   int* pleft;            // [n_jobs][part_cap]
   double* mpart;         // [n_jobs][pred_chunks] per-CTA metric partial sums
   double* trace;         // [n_inds][num_boost_round] or null

@@ -105,6 +105,7 @@ struct FoldSet {
   std::vector<std::vector<uint32_t>> rows;   // fold order: train slice then test slice
   std::vector<DevBuf<uint32_t>> d_rows;
   std::vector<DevBuf<uint8_t>> d_bins;
+  std::vector<DevBuf<uint8_t>> d_bins_col;
   std::vector<DevBuf<float>> d_y;
   DevBuf<float> d_cuts;                       // [nfold][f][256]
   DevBuf<int> d_ncuts;                        // [nfold][f]
@@ -158,7 +159,7 @@ int prepare_impl(gt_engine* e, int nfold, FoldSet** out) {
   fs->perm.resize(n); fs->fold_begin.resize(nfold + 1);
   make_folds_host(n, nfold, 0u, fs->perm.data(), fs->fold_begin.data());
   fs->ntrain.resize(nfold); fs->ntest.resize(nfold); fs->rows.resize(nfold);
-  fs->d_rows.resize(nfold); fs->d_bins.resize(nfold); fs->d_y.resize(nfold);
+  fs->d_rows.resize(nfold); fs->d_bins.resize(nfold); fs->d_bins_col.resize(nfold); fs->d_y.resize(nfold);
   fs->sum_not1_sq.assign(nfold, 0); fs->sum_not1_lg.assign(nfold, 0); fs->n1.assign(nfold, 0); fs->nnot1.assign(nfold, 0);
   cudaEvent_t ev0, ev1;
   GT_CUDA(cudaEventCreate(&ev0)); GT_CUDA(cudaEventCreate(&ev1));
@@ -239,9 +240,12 @@ int prepare_impl(gt_engine* e, int nfold, FoldSet** out) {
     gt::launch_bin(e->d_X, e->ldx, f, e->fpad, fs->d_rows[k].p, n, fs->d_cuts.p + (size_t)k * f * GT_MAX_BIN,
                    fs->d_ncuts.p + (size_t)k * f, fs->d_bins[k].p, e->stream);
     GT_CUDA(cudaGetLastError());
+    GT_CUDA(fs->d_bins_col[k].ensure((size_t)n * f));
+    gt::launch_bins_to_columns(fs->d_bins[k].p, f, e->fpad, n, fs->d_bins_col[k].p, e->stream);
+    GT_CUDA(cudaGetLastError());
     gt::launch_gather_y(e->d_y, fs->d_rows[k].p, n, fs->d_y[k].p, e->stream);
     GT_CUDA(cudaGetLastError());
-    h_folds[k].bins = fs->d_bins[k].p; h_folds[k].y = fs->d_y[k].p;
+    h_folds[k].bins = fs->d_bins[k].p; h_folds[k].bins_col = fs->d_bins_col[k].p; h_folds[k].y = fs->d_y[k].p;
     h_folds[k].cuts = fs->d_cuts.p + (size_t)k * f * GT_MAX_BIN; h_folds[k].ncuts = fs->d_ncuts.p + (size_t)k * f;
     h_folds[k].ntrain = fs->ntrain[k]; h_folds[k].ntest = fs->ntest[k];
   }
@@ -342,7 +346,7 @@ int eval_impl(gt_engine* e, int n_ind, const double* genes, const gt_fit_opts* o
     b += hist_cells_for_depth(D, e->groups) * sizeof(gt::HistEntry);
     b += (size_t)gt::kNodeCap * (sizeof(gt::Node) + sizeof(gt::TreeNode));
     b += (size_t)hist_cap * (sizeof(gt::HistItem) + 4) + (size_t)pair_cap * sizeof(gt::PairRec);
-    b += (size_t)part_cap * (sizeof(gt::PartItem) + gt::kPartRows / 8 + 4) + (size_t)pred_chunks * 8;
+    b += (size_t)part_cap * (sizeof(gt::PartItem) + 4) + (size_t)pred_chunks * 8;
     b += sizeof(gt::JobParams) + sizeof(gt::JobState);
     return b;
   };
@@ -374,7 +378,7 @@ int eval_impl(gt_engine* e, int n_ind, const double* genes, const gt_fit_opts* o
   DevBuf<gt::JobParams> d_jp; DevBuf<gt::JobState> d_js; DevBuf<gt::IndState> d_is;
   DevBuf<gt::Node> d_nodes; DevBuf<gt::TreeNode> d_tree; DevBuf<float> d_pred; DevBuf<int2> d_gq;
   DevBuf<uint32_t> d_ridx; DevBuf<gt::HistEntry> d_hist; DevBuf<gt::HistItem> d_hitems; DevBuf<int> d_zlist;
-  DevBuf<gt::PairRec> d_pairs; DevBuf<gt::PartItem> d_pitems; DevBuf<uint32_t> d_pbits; DevBuf<int> d_pleft;
+  DevBuf<gt::PairRec> d_pairs; DevBuf<gt::PartItem> d_pitems; DevBuf<int> d_pleft;
   DevBuf<double> d_mpart; DevBuf<double> d_trace; DevBuf<unsigned long long> d_counters;
   DevBuf<double> d_fit; DevBuf<int> d_rounds; DevBuf<gt_tree_node> d_trees; DevBuf<gt_node_rows> d_nrows;
   GT_CUDA(d_jp.ensure(max_jobs)); GT_CUDA(d_js.ensure(max_jobs)); GT_CUDA(d_is.ensure(max_inds));
@@ -383,7 +387,7 @@ int eval_impl(gt_engine* e, int n_ind, const double* genes, const gt_fit_opts* o
   GT_CUDA(d_ridx.ensure(max_jobs * 2 * (size_t)nt_stride)); GT_CUDA(d_hist.ensure(max_hist));
   GT_CUDA(d_hitems.ensure(max_jobs * hist_cap)); GT_CUDA(d_zlist.ensure(max_jobs * hist_cap));
   GT_CUDA(d_pairs.ensure(max_jobs * pair_cap)); GT_CUDA(d_pitems.ensure(max_jobs * part_cap));
-  GT_CUDA(d_pbits.ensure(max_jobs * (size_t)part_cap * (gt::kPartRows / 32))); GT_CUDA(d_pleft.ensure(max_jobs * part_cap));
+  GT_CUDA(d_pleft.ensure(max_jobs * part_cap));
   GT_CUDA(d_mpart.ensure(max_jobs * pred_chunks)); GT_CUDA(d_counters.ensure(8));
   GT_CUDA(d_fit.ensure(n_ind)); GT_CUDA(d_rounds.ensure(n_ind));
   const bool want_trace = dump && dump->trace_means;
@@ -467,7 +471,7 @@ int eval_impl(gt_engine* e, int n_ind, const double* genes, const gt_fit_opts* o
     w.folds = fs->d_folds.p; w.grp_maxnc = fs->d_grp_maxnc.p;
     w.jp = d_jp.p; w.js = d_js.p; w.is = d_is.p; w.nodes = d_nodes.p; w.tree = d_tree.p; w.pred = d_pred.p;
     w.gq = d_gq.p; w.ridx = d_ridx.p; w.hist = d_hist.p; w.hitems = d_hitems.p; w.zlist = d_zlist.p;
-    w.pairs = d_pairs.p; w.pitems = d_pitems.p; w.pbits = d_pbits.p; w.pleft = d_pleft.p; w.mpart = d_mpart.p;
+    w.pairs = d_pairs.p; w.pitems = d_pitems.p; w.pleft = d_pleft.p; w.mpart = d_mpart.p;
     w.trace = want_trace ? d_trace.p : nullptr; w.counters = d_counters.p;
 
     gt::launch_init_wave(w, e->stream); ++launches;

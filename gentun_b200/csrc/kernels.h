@@ -22,6 +22,7 @@ void launch_sketch(const float* X, long long ldx, int f, int nfold, const uint32
                    int count, cudaStream_t s);
 void launch_bin(const float* X, long long ldx, int f, int fpad, const uint32_t* rows, long long n,
                 const float* cuts, const int* ncuts, uint8_t* bins, cudaStream_t s);
+void launch_bins_to_columns(const uint8_t* bins, int f, int fpad, long long n, uint8_t* out, cudaStream_t s);
 void launch_gather_y(const float* y, const uint32_t* rows, long long n, float* out, cudaStream_t s);
 
 // boost.cu

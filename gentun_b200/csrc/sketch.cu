@@ -331,6 +331,15 @@ __global__ void k_bin_u8(const float* __restrict__ X, long long ldx, int f, int 
   }
 }
 
+// feature-major copy of the bin matrix: out[j][r] = bins[r][j]
+__global__ void k_bins_to_columns(const uint8_t* __restrict__ bins, int f, int fpad, long long n, uint8_t* __restrict__ out) {
+  const long long total = n * f;
+  for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+    const long long j = t / n, r = t % n;
+    out[t] = bins[(size_t)r * fpad + j];
+  }
+}
+
 __global__ void k_gather_y(const float* __restrict__ y, const uint32_t* __restrict__ rows, long long n, float* __restrict__ out) {
   for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) out[t] = y[rows[t]];
 }
@@ -351,6 +360,10 @@ void launch_bin(const float* X, long long ldx, int f, int fpad, const uint32_t* 
   int blocks = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
   if (blocks < 1) blocks = 1;
   k_bin_u8<<<blocks, 256, 0, s>>>(X, ldx, f, fpad, rows, n, cuts, ncuts, bins);
+}
+
+void launch_bins_to_columns(const uint8_t* bins, int f, int fpad, long long n, uint8_t* out, cudaStream_t s) {
+  k_bins_to_columns<<<148 * 16, 256, 0, s>>>(bins, f, fpad, n, out);
 }
 
 void launch_gather_y(const float* y, const uint32_t* rows, long long n, float* out, cudaStream_t s) {
