@@ -568,6 +568,10 @@ int eval_impl(gt_engine* e, int n_ind, const double* genes, const gt_fit_opts* o
 
 }  // namespace
 
+namespace gt {
+void set_error_message(const char* msg) { g_err = msg ? msg : ""; }
+}  // namespace gt
+
 extern "C" {
 
 int gt_engine_create(const float* X, int64_t n, int32_t f, int64_t ldx, const float* y, const gt_data_opts* opts,

@@ -25,6 +25,9 @@ void launch_bin(const float* X, long long ldx, int f, int fpad, const uint32_t* 
 void launch_bins_to_columns(const uint8_t* bins, int f, int fpad, long long n, uint8_t* out, cudaStream_t s);
 void launch_gather_y(const float* y, const uint32_t* rows, long long n, float* out, cudaStream_t s);
 
+// engine.cu: message returned by gt_last_error() for the calling thread
+void set_error_message(const char* msg);
+
 // boost.cu
 void launch_init_wave(const Wave& w, cudaStream_t s);
 void launch_grad(const Wave& w, cudaStream_t s);

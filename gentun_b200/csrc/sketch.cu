@@ -7,6 +7,9 @@
 // order-dependent streaming algorithm; it is reproduced stream by stream (one CTA per
 // fold x feature), with the queue fill expressed as a run-length scan and the queue sort as a
 // CTA-wide bitonic network, and the summary merge/prune hierarchy walked by one thread.
+#include <cmath>
+#include <cstdio>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -373,3 +376,114 @@ void launch_gather_y(const float* y, const uint32_t* rows, long long n, float* o
 }
 
 }  // namespace gt
+
+// =====================================================================================================
+// Allocation-free cut points for one column (gt_column_cuts_noalloc, include/gentun_b200.h).
+//
+// Who this is for: code that must not touch the device allocator when it asks for cut points -- a
+// serving loop that re-bins a drifting feature while other streams are busy (cudaMalloc / cudaFree
+// synchronise the whole device), a process running under a fixed memory reservation where a late
+// allocation can fail, or a library hook that is only allowed to enqueue work.  gt_engine_prepare
+// allocates its sketch arenas with cudaMalloc; this entry point runs the same k_sketch_cuts kernel
+// for a single stream with every byte of scratch (row ids, sort keys, summary levels) taken from the
+// fixed array below, which each GPU that loads the library keeps resident until the process exits.
+// The price is a hard size limit (kNoAllocMaxRows values per call) and no concurrency: all calls share
+// the one array, so two calls that overlap on the GPU (different streams, or different host threads
+// on different streams) corrupt each other.  Calls on one stream are safe back to back: the kernel
+// clears its sort keys and level sizes on entry and the set-up kernel rewrites the header and row ids.
+namespace gt {
+namespace {
+
+constexpr long long kNoAllocMaxRows = 65536;
+// LimitSizeLevel at 65536 rows and eps = 1/2048 gives limit_size 8193 over 4 levels; smaller inputs need less
+constexpr int kNaLimitMax = 8193;
+constexpr int kNaLevelAlloc = 4 + 3;
+constexpr int kNaBufCap = 2 * kNaLimitMax + 2;
+constexpr int kNaKeys = 32768;                                                       // power of two >= 2 * 8193
+constexpr long long kNaEntries = 3ll * kNaBufCap + (long long)kNaLevelAlloc * kNaLimitMax;
+constexpr size_t kNaRowsOff = 256;                                                   // header: rows pointer, count, limit
+constexpr size_t kNaKeysOff = kNaRowsOff + (size_t)kNoAllocMaxRows * sizeof(uint32_t);
+constexpr size_t kNaEntsOff = kNaKeysOff + (size_t)kNaKeys * sizeof(unsigned long long);
+constexpr size_t kNaBytes = kNaEntsOff + (size_t)kNaEntries * sizeof(float4);       // about 2.2 MB
+static_assert(kNaKeysOff % 256 == 0 && kNaEntsOff % 256 == 0, "scratch sections must stay 256-byte aligned");
+
+static __device__ __align__(256) unsigned char g_cut_scratch[kNaBytes];
+
+// device code may name the array directly; host code needs the address from cudaGetSymbolAddress
+__global__ void k_noalloc_setup(long long n, int limit) {
+  uint32_t* rows = reinterpret_cast<uint32_t*>(g_cut_scratch + kNaRowsOff);
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) rows[i] = (uint32_t)i;
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    *reinterpret_cast<const uint32_t**>(g_cut_scratch) = rows;     // the kernel's fold_rows[0]
+    *reinterpret_cast<long long*>(g_cut_scratch + 8) = n;          // fold_ntrain[0]
+    *reinterpret_cast<int*>(g_cut_scratch + 16) = limit;           // fold_limit[0]
+  }
+}
+
+unsigned char* g_scratch_on_device[64] = {nullptr};   // per device, filled at first use
+
+void na_limit_size_level(size_t maxn, double eps, size_t* nlevel, size_t* limit) {
+  *nlevel = 1;
+  for (;;) {
+    *limit = (size_t)ceil((double)*nlevel / eps) + 1;
+    if (maxn < *limit) *limit = maxn;
+    if (((size_t)1 << *nlevel) * *limit >= maxn) break;
+    ++*nlevel;
+  }
+}
+
+int na_fail(int code, const char* what, const char* detail = "") {
+  char buf[512];
+  snprintf(buf, sizeof(buf), "gt_column_cuts_noalloc: %s%s", what, detail);
+  set_error_message(buf);
+  return code;
+}
+
+}  // namespace
+}  // namespace gt
+
+extern "C" int gt_column_cuts_noalloc(const float* d_values, int64_t n, float* d_cuts, int32_t* d_ncuts, void* stream) {
+  using namespace gt;
+  char msg[256];
+  if (!d_values || !d_cuts || !d_ncuts) return na_fail(GT_ERR_ARG, "null pointer");
+  if (n < 1 || n > kNoAllocMaxRows) {
+    snprintf(msg, sizeof(msg), "n=%lld is outside 1..%lld, the capacity of the fixed scratch array", (long long)n, kNoAllocMaxRows);
+    return na_fail(GT_ERR_ARG, msg);
+  }
+  int dev = 0;
+  cudaError_t ce = cudaGetDevice(&dev);
+  if (ce != cudaSuccess) return na_fail(GT_ERR_CUDA, "cudaGetDevice failed: ", cudaGetErrorString(ce));
+  if (dev < 0 || dev >= 64) return na_fail(GT_ERR_ARG, "device ordinal above 63 is not supported");
+  if (!g_scratch_on_device[dev]) {
+    // once per device, with that device current: the host-side name of a __device__ array is not a device address
+    void* p = nullptr;
+    ce = cudaGetSymbolAddress(&p, g_cut_scratch);
+    if (ce != cudaSuccess || !p) return na_fail(GT_ERR_CUDA, "cudaGetSymbolAddress failed: ", cudaGetErrorString(ce));
+    g_scratch_on_device[dev] = static_cast<unsigned char*>(p);
+  }
+  unsigned char* base = g_scratch_on_device[dev];
+  const size_t n_bins = (size_t)(n < GT_MAX_BIN ? n : GT_MAX_BIN);
+  const double eps = 1.0 / (double)((float)n_bins * 8.0f);
+  size_t nlevel, limit;
+  na_limit_size_level((size_t)n, eps, &nlevel, &limit);
+  SketchPlan plan;
+  plan.buf_cap = (int)(2 * limit + 2);
+  plan.nlevel_alloc = (int)nlevel + 3;
+  int kp = 2; while (kp < (int)(2 * limit)) kp <<= 1;
+  plan.keys_per_stream = kp;
+  plan.entries_per_stream = 3ll * plan.buf_cap + (long long)plan.nlevel_alloc * (long long)limit;
+  if ((long long)limit > kNaLimitMax || plan.nlevel_alloc > kNaLevelAlloc || kp > kNaKeys || plan.entries_per_stream > kNaEntries)
+    return na_fail(GT_ERR_ARG, "this n needs more scratch than the fixed array holds");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int blocks = (int)((n + 255) / 256 < 64 ? (n + 255) / 256 : 64);
+  k_noalloc_setup<<<blocks, 256, 0, s>>>((long long)n, (int)limit);
+  k_sketch_cuts<<<1, kSketchThreads, 0, s>>>(d_values, 1, 1, 1, reinterpret_cast<const uint32_t* const*>(base),
+                                             reinterpret_cast<const long long*>(base + 8), plan, reinterpret_cast<const int*>(base + 16),
+                                             reinterpret_cast<unsigned long long*>(base + kNaKeysOff),
+                                             reinterpret_cast<float4*>(base + kNaEntsOff), d_cuts, d_ncuts, 0);
+  ce = cudaGetLastError();
+  if (ce != cudaSuccess) return na_fail(GT_ERR_CUDA, "kernel launch failed: ", cudaGetErrorString(ce));
+  return GT_OK;
+}
+
+extern "C" int64_t gt_column_cuts_noalloc_max_rows(void) { return gt::kNoAllocMaxRows; }

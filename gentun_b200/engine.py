@@ -57,7 +57,8 @@ _lib_lock = threading.Lock()
 
 EXPORTS = ("gt_engine_create", "gt_engine_prepare", "gt_engine_eval", "gt_engine_eval_ex", "gt_engine_destroy",
            "gt_engine_fold_sizes", "gt_engine_get_fold_rows", "gt_engine_get_cuts", "gt_engine_get_bins",
-           "gt_engine_get_stats", "gt_make_folds", "gt_last_error", "gt_version")
+           "gt_engine_get_stats", "gt_make_folds", "gt_last_error", "gt_version",
+           "gt_column_cuts_noalloc", "gt_column_cuts_noalloc_max_rows")
 
 
 def load_library():
@@ -86,6 +87,8 @@ def load_library():
         L.gt_make_folds.argtypes = [i64, i32, C.c_uint32, vp, vp]
         L.gt_last_error.restype = C.c_char_p
         L.gt_version.restype = C.c_int
+        L.gt_column_cuts_noalloc.argtypes = [vp, i64, vp, vp, vp]
+        L.gt_column_cuts_noalloc_max_rows.restype = i64
         _lib = L
         return _lib
 

@@ -130,6 +130,21 @@ int gt_engine_get_stats(gt_engine* e, gt_stats* out);
  * (xgboost training.py mknfold as called from xgboost_models.py:33-36). perm [n]; fold_begin [nfold+1]. */
 int gt_make_folds(int64_t n, int32_t nfold, uint32_t seed, int64_t* perm, int64_t* fold_begin);
 
+/* No counterpart in the reference (gentun never manages device memory).  Cut points of ONE column for
+ * callers that may not allocate: a serving loop re-binning a feature while other streams run (cudaMalloc
+ * and cudaFree stall the whole device), a process under a fixed memory reservation, a hook that may only
+ * enqueue work.  Same sketch kernel as gt_engine_prepare, but every byte of scratch comes from a fixed
+ * __device__ array inside the library (about 2.2 MB per GPU, held until exit) -- no cudaMalloc, no
+ * cudaFree, no allocating library call.  d_values [n] (device, the column in DMatrix row order),
+ * d_cuts [GT_MAX_BIN] and d_ncuts [1] (device) are the caller's; work is enqueued on `stream`
+ * (a cudaStream_t, NULL = default stream) and the call returns without synchronising.
+ * Limits: 1 <= n <= gt_column_cuts_noalloc_max_rows() (65536), else GT_ERR_ARG.  All calls share the
+ * one scratch array: issue them on one stream, or otherwise keep them from overlapping on the GPU --
+ * overlapping calls race.  The first call on each device looks the array's address up
+ * (cudaGetSymbolAddress); make that first call before any stream capture begins. */
+int gt_column_cuts_noalloc(const float* d_values, int64_t n, float* d_cuts, int32_t* d_ncuts, void* stream);
+int64_t gt_column_cuts_noalloc_max_rows(void);
+
 const char* gt_last_error(void);
 int gt_version(void);
 
