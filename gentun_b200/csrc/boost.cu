@@ -52,6 +52,22 @@ __device__ __forceinline__ float split_gain(const JobParams& p, double GL, doubl
   float wl = calc_weight(p, GL, HL), wr = calc_weight(p, GR, HR);
   return gain_given_weight(p, GL, HL, wl) + gain_given_weight(p, GR, HR, wr);
 }
+// fp32 estimate of split_gain - root_gain's first two terms (same formulas, float throughout);
+// mag returns the size of the terms, from which the caller bounds the estimate's rounding error
+__device__ __forceinline__ float gain_term_est(const JobParams& p, float G, float H) {
+  if (H <= 0.f) return 0.f;   // callers pass only candidates whose children already satisfy min_child_weight
+  const float t = G > p.alpha ? G - p.alpha : (G < -p.alpha ? G + p.alpha : 0.f);
+  const float d = H + p.lambda;
+  if (p.mds == 0.0f) return __fdividef(t * t, d);
+  float w = -__fdividef(t, d);
+  if (fabsf(w) > p.mds) w = copysignf(p.mds, w);
+  return -(2.0f * G * w + d * (w * w));
+}
+__device__ __forceinline__ float split_gain_est(const JobParams& p, float GL, float HL, float GR, float HR, float& mag) {
+  const float a = gain_term_est(p, GL, HL), b = gain_term_est(p, GR, HR);
+  mag = fabsf(a) + fabsf(b);
+  return a + b;
+}
 __device__ __forceinline__ float sigmoid_x(float x) {   // upstream common::Sigmoid
   x = fminf(-x, 88.7f);
   float denom = expf(x) + 1.0f + 1e-16f;
@@ -535,21 +551,84 @@ __global__ void __launch_bounds__(1024) k_scan(Wave w, int level) {
   }
   s_sum[warp][lane] = acc;
   __syncthreads();
-  Cand best{0.0f, -1, -1, 0, 0};
-  if (live && factive) {
-    long long GL = 0, HL = 0;
-    for (int k = 0; k < ch; ++k) { const longlong2 t = s_sum[warp - ch + k][lane]; GL += t.x; HL += t.y; }
-    const int hi = min(b_hi, nc);
+  // Pass 2a: a cheap fp32 estimate of every candidate's gain.  Only candidates whose estimate is within
+  // the estimate's error margin of the best one can be the exact argmax; pass 2b re-evaluates just those
+  // in the reference's double/float expression order.  (FP64 evaluation of all candidates made this
+  // kernel compute-bound at the deep levels.)
+  const long long hmin_q = (long long)ceil((double)jp.mcw * (double)js.sh);   // hl >= mcw  <=>  HL_q >= mcw * sh (exact)
+  long long GL0 = 0, HL0 = 0;
+  if (live && factive)
+    for (int k = 0; k < ch; ++k) { const longlong2 t = s_sum[warp - ch + k][lane]; GL0 += t.x; HL0 += t.y; }
+  const int hi = (live && factive) ? min(b_hi, nc) : b_lo;
+  const float isg = (float)inv_sg, ish = (float)inv_sh;
+  const float Gt_f = (float)Gt * isg, Ht_f = (float)Ht * ish;
+  float amax = -3.0e38f, smax = 0.0f;
+  float e1 = -3.0e38f, e2 = -3.0e38f;   // this lane's best and second-best estimate
+  int b1 = -1;
+  long long GL1 = 0, HL1 = 0;
+  {
+    long long GL = GL0, HL = HL0;
     for (int b = b_lo; b < hi; ++b) {
       longlong2 e = load_cell(hbuilt, nar_b, goff + (size_t)b * kLanes);
       if (!is_built) { const longlong2 pe = load_cell(hpar, nar_p, goff + (size_t)b * kLanes); e.x = pe.x - e.x; e.y = pe.y - e.y; }
       GL += e.x; HL += e.y;
-      if (e.x != 0 || e.y != 0) {   // an empty bin repeats the previous candidate, which never wins (strict >)
-        const double gl = (double)GL * inv_sg, hl = (double)HL * inv_sh;
-        const double gr = (double)(Gt - GL) * inv_sg, hr = (double)(Ht - HL) * inv_sh;
-        if (hl >= jp.mcw && hr >= jp.mcw) {
-          const float chg = split_gain(jp, gl, hl, gr, hr) - root_gain;
-          if (!isinf(chg) && chg > best.chg) { best.chg = chg; best.f = f; best.b = b; best.GL = GL; best.HL = HL; }
+      if ((e.x != 0 || e.y != 0) && HL >= hmin_q && (Ht - HL) >= hmin_q) {
+        float mag;
+        const float gl = (float)GL * isg, hl = (float)HL * ish;
+        const float est = split_gain_est(jp, gl, hl, Gt_f - gl, Ht_f - hl, mag);
+        smax = fmaxf(smax, mag);
+        if (est > e1) { e2 = e1; e1 = est; b1 = b; GL1 = GL; HL1 = HL; }
+        else if (est > e2) e2 = est;
+      }
+    }
+    amax = e1;
+  }
+  for (int d = 16; d; d >>= 1) {
+    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, d));
+    smax = fmaxf(smax, __shfl_xor_sync(0xffffffffu, smax, d));
+  }
+  __shared__ float s_est[32][2];
+  if (lane == 0) { s_est[warp][0] = amax; s_est[warp][1] = smax; }
+  __syncthreads();
+  {
+    const int w0 = c * G * NCH;
+    amax = -3.0e38f; smax = 0.0f;
+    for (int k = 0; k < G * NCH; ++k) { amax = fmaxf(amax, s_est[w0 + k][0]); smax = fmaxf(smax, s_est[w0 + k][1]); }
+  }
+  // estimate error: a few fp32 roundings on terms of size <= smax (the right-hand sums are formed by an
+  // fp32 subtraction from the node totals), plus the root gain
+  const float margin = 3.2e-5f * (smax + fabsf(root_gain)) + 1e-12f;
+  // a candidate can win only with est close to the best estimate and with a positive gain (est > root gain)
+  const float cut = fmaxf(amax, root_gain) - 2.0f * margin;
+  Cand best{0.0f, -1, -1, 0, 0};
+  if (e1 >= cut) {
+    if (e2 < cut) {
+      // the usual case: one candidate of this lane survives; evaluate it exactly from the saved prefix
+      const double gl = (double)GL1 * inv_sg, hl = (double)HL1 * inv_sh;
+      const double gr = (double)(Gt - GL1) * inv_sg, hr = (double)(Ht - HL1) * inv_sh;
+      if (hl >= jp.mcw && hr >= jp.mcw) {
+        const float chg = split_gain(jp, gl, hl, gr, hr) - root_gain;
+        if (!isinf(chg) && chg > best.chg) { best.chg = chg; best.f = f; best.b = b1; best.GL = GL1; best.HL = HL1; }
+      }
+    } else {
+      // several near-ties in this lane: walk the bins again in scan order
+      long long GL = GL0, HL = HL0;
+      for (int b = b_lo; b < hi; ++b) {
+        longlong2 e = load_cell(hbuilt, nar_b, goff + (size_t)b * kLanes);
+        if (!is_built) { const longlong2 pe = load_cell(hpar, nar_p, goff + (size_t)b * kLanes); e.x = pe.x - e.x; e.y = pe.y - e.y; }
+        GL += e.x; HL += e.y;
+        if ((e.x != 0 || e.y != 0) && HL >= hmin_q && (Ht - HL) >= hmin_q) {   // an empty bin repeats the previous candidate (strict >)
+          float mag;
+          const float glf = (float)GL * isg, hlf = (float)HL * ish;
+          const float est = split_gain_est(jp, glf, hlf, Gt_f - glf, Ht_f - hlf, mag);
+          if (est >= cut) {
+            const double gl = (double)GL * inv_sg, hl = (double)HL * inv_sh;
+            const double gr = (double)(Gt - GL) * inv_sg, hr = (double)(Ht - HL) * inv_sh;
+            if (hl >= jp.mcw && hr >= jp.mcw) {
+              const float chg = split_gain(jp, gl, hl, gr, hr) - root_gain;
+              if (!isinf(chg) && chg > best.chg) { best.chg = chg; best.f = f; best.b = b; best.GL = GL; best.HL = HL; }
+            }
+          }
         }
       }
     }
