@@ -14,6 +14,8 @@
 // |q| <= 2^19) so that all histogram arithmetic is integer: shared-memory partials are int32
 // (native ATOMS.ADD), global cells are int64, parent - child subtraction is exact and the result
 // does not depend on summation order.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -372,12 +374,22 @@ __device__ __forceinline__ void hist_accumulate(const uint4 v, const int2 g2, bo
   r[1] = __funnelshift_r(u1, u2, rb);
   r[2] = __funnelshift_r(u2, u3, rb);
   r[3] = __funnelshift_r(u3, u0, rb);
+  // addresses of eight steps first, then their sixteen reductions: an in-flight RED still holds its address
+  // register, so reusing one or two registers for every step stalls the next address computation
 #pragma unroll
-  for (int s = 0; s < 16; ++s) {
-    const uint32_t bin = __byte_perm(r[s >> 2], 0u, 0x4440u + (uint32_t)(s & 3));
-    const uint32_t cell = bin * (kLanes * 4u) + cs[s];
-    red_shared(cell, g2.x);
-    red_shared_hi(cell, g2.y);
+  for (int half = 0; half < 2; ++half) {
+    uint32_t cell[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int s = half * 8 + k;
+      const uint32_t bin = __byte_perm(r[s >> 2], 0u, 0x4440u + (uint32_t)(s & 3));
+      cell[k] = bin * (kLanes * 4u) + cs[s];
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      red_shared(cell[k], g2.x);
+      red_shared_hi(cell[k], g2.y);
+    }
   }
 }
 
@@ -988,7 +1000,8 @@ void launch_plan_hist(const Wave& w, int level, cudaStream_t s) { k_plan_hist<<<
 void launch_hist_zero(const Wave& w, int level, cudaStream_t s) { k_hist_zero<<<dim3(32, w.n_jobs), 256, 0, s>>>(w, level); }
 void launch_hist(const Wave& w, int level, cudaStream_t s) {
   int cap = hist_items_bound(w, level);
-  if (w.groups % 2 == 0) k_hist<4><<<dim3(cap * (w.groups / 2), w.n_jobs), 512, 2 * kHistSmem, s>>>(w, level);
+  static const bool force_single = getenv("GT_HIST_SINGLE_GROUP") != nullptr;   // tuning switch
+  if (w.groups % 2 == 0 && !force_single) k_hist<4><<<dim3(cap * (w.groups / 2), w.n_jobs), 512, 2 * kHistSmem, s>>>(w, level);
   else k_hist<2><<<dim3(cap * w.groups, w.n_jobs), 256, kHistSmem, s>>>(w, level);
 }
 void launch_scan(const Wave& w, int level, cudaStream_t s) {

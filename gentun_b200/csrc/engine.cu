@@ -118,6 +118,17 @@ struct FoldSet {
   double prepare_ms = 0;
 };
 
+// device buffers of gt_engine_eval, kept between calls (cudaMalloc / cudaFree of several GB per call
+// cost more host time than a whole wave of kernels)
+struct EvalBuffers {
+  DevBuf<gt::JobParams> d_jp; DevBuf<gt::JobState> d_js; DevBuf<gt::IndState> d_is;
+  DevBuf<gt::Node> d_nodes; DevBuf<gt::TreeNode> d_tree; DevBuf<float> d_pred; DevBuf<int2> d_gq;
+  DevBuf<uint32_t> d_ridx; DevBuf<gt::HistEntry> d_hist; DevBuf<gt::HistItem> d_hitems; DevBuf<int> d_zlist;
+  DevBuf<gt::PairRec> d_pairs; DevBuf<gt::PartItem> d_pitems; DevBuf<int> d_pleft;
+  DevBuf<double> d_mpart; DevBuf<double> d_trace; DevBuf<unsigned long long> d_counters;
+  DevBuf<double> d_fit; DevBuf<int> d_rounds; DevBuf<gt_tree_node> d_trees; DevBuf<gt_node_rows> d_nrows;
+};
+
 }  // namespace
 
 struct gt_engine {
@@ -132,6 +143,7 @@ struct gt_engine {
   int64_t mem_budget = 0;
   int collect_timing = 0;
   std::map<int, std::unique_ptr<FoldSet>> foldsets;
+  EvalBuffers bufs;
   gt_stats stats{};
 };
 
@@ -352,7 +364,9 @@ int eval_impl(gt_engine* e, int n_ind, const double* genes, const gt_fit_opts* o
   };
   size_t free_b = 0, total_b = 0;
   GT_CUDA(cudaMemGetInfo(&free_b, &total_b));
-  size_t budget = e->mem_budget > 0 ? (size_t)e->mem_budget : (size_t)(0.85 * (double)free_b);
+  size_t held = 0;   // buffers kept from the previous call are reusable
+  held += e->bufs.d_pred.count * 4 + e->bufs.d_gq.count * 8 + e->bufs.d_ridx.count * 4 + e->bufs.d_hist.count * sizeof(gt::HistEntry);
+  size_t budget = e->mem_budget > 0 ? (size_t)e->mem_budget : (size_t)(0.85 * (double)(free_b + held));
   std::vector<std::pair<int, int>> waves;   // [begin, end) in `order`
   {
     int b = 0;
@@ -375,12 +389,12 @@ int eval_impl(gt_engine* e, int n_ind, const double* genes, const gt_fit_opts* o
     for (int q = wv.first; q < wv.second; ++q) hc += hist_cells_for_depth((int)genes[(size_t)order[q] * GT_NUM_GENES + 2], e->groups) * nfold;
     max_inds = std::max(max_inds, inds); max_jobs = std::max(max_jobs, inds * nfold); max_hist = std::max(max_hist, hc);
   }
-  DevBuf<gt::JobParams> d_jp; DevBuf<gt::JobState> d_js; DevBuf<gt::IndState> d_is;
-  DevBuf<gt::Node> d_nodes; DevBuf<gt::TreeNode> d_tree; DevBuf<float> d_pred; DevBuf<int2> d_gq;
-  DevBuf<uint32_t> d_ridx; DevBuf<gt::HistEntry> d_hist; DevBuf<gt::HistItem> d_hitems; DevBuf<int> d_zlist;
-  DevBuf<gt::PairRec> d_pairs; DevBuf<gt::PartItem> d_pitems; DevBuf<int> d_pleft;
-  DevBuf<double> d_mpart; DevBuf<double> d_trace; DevBuf<unsigned long long> d_counters;
-  DevBuf<double> d_fit; DevBuf<int> d_rounds; DevBuf<gt_tree_node> d_trees; DevBuf<gt_node_rows> d_nrows;
+  EvalBuffers& B = e->bufs;
+  auto &d_jp = B.d_jp; auto &d_js = B.d_js; auto &d_is = B.d_is; auto &d_nodes = B.d_nodes; auto &d_tree = B.d_tree;
+  auto &d_pred = B.d_pred; auto &d_gq = B.d_gq; auto &d_ridx = B.d_ridx; auto &d_hist = B.d_hist; auto &d_hitems = B.d_hitems;
+  auto &d_zlist = B.d_zlist; auto &d_pairs = B.d_pairs; auto &d_pitems = B.d_pitems; auto &d_pleft = B.d_pleft;
+  auto &d_mpart = B.d_mpart; auto &d_trace = B.d_trace; auto &d_counters = B.d_counters; auto &d_fit = B.d_fit;
+  auto &d_rounds = B.d_rounds; auto &d_trees = B.d_trees; auto &d_nrows = B.d_nrows;
   GT_CUDA(d_jp.ensure(max_jobs)); GT_CUDA(d_js.ensure(max_jobs)); GT_CUDA(d_is.ensure(max_inds));
   GT_CUDA(d_nodes.ensure(max_jobs * gt::kNodeCap)); GT_CUDA(d_tree.ensure(max_jobs * gt::kNodeCap));
   GT_CUDA(d_pred.ensure(max_jobs * (size_t)n)); GT_CUDA(d_gq.ensure(max_jobs * (size_t)nt_stride));
