@@ -39,7 +39,8 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
-    ap.add_argument("--inds-per-step", type=int, default=8, help="individuals per step per GPU")
+    ap.add_argument("--inds-per-step", type=int, default=32,
+                    help="individuals per step per GPU (32 = one GPU's share of the 256-individual generation on 8 GPUs)")
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--cpu-rounds", type=int, default=2, help="boosting rounds in the CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
