@@ -401,16 +401,18 @@ __device__ __forceinline__ void hist_flush(const Wave& w, const JobParams& jp, i
                                            bool atomic, bool rezero) {
   constexpr int kThreads = UNITS == 2 ? 256 : 512;
   constexpr int kGroupsPerCta = UNITS / 2;
-  HistEntry* dst = node_hist(w, jp, level, it.node) + (size_t)cg * kGroupsPerCta * (kBins * kLanes);
+  HistEntry* slot = node_hist(w, jp, level, it.node);
+  const size_t c0 = (size_t)cg * kGroupsPerCta * (kBins * kLanes);   // first cell of this CTA's groups inside the node
   for (int i = threadIdx.x; i < kGroupsPerCta * kBins * kLanes; i += kThreads) {
     const int gsel = i / (kBins * kLanes), cell = i % (kBins * kLanes);
     int* pg = sh + gsel * (2 * kBins * kLanes) + cell;
     const int g = pg[0], h = pg[kBins * kLanes];
     if (atomic) {
-      if (g) atomicAdd(reinterpret_cast<unsigned long long*>(&dst[i].g), (unsigned long long)(long long)g);
-      if (h) atomicAdd(reinterpret_cast<unsigned long long*>(&dst[i].h), (unsigned long long)(long long)h);
+      if (g) atomicAdd(reinterpret_cast<unsigned long long*>(&slot[c0 + i].g), (unsigned long long)(long long)g);
+      if (h) atomicAdd(reinterpret_cast<unsigned long long*>(&slot[c0 + i].h), (unsigned long long)(long long)h);
     } else {
-      reinterpret_cast<int2*>(dst)[i] = make_int2(g, h);   // single-CTA node (<= kEpochRows rows): narrow format
+      // single-CTA node (<= kEpochRows rows): narrow format, cells are int32 pairs packed from the slot base
+      reinterpret_cast<int2*>(slot)[c0 + i] = make_int2(g, h);
     }
     if (rezero) { pg[0] = 0; pg[kBins * kLanes] = 0; }
   }

@@ -157,6 +157,192 @@ __device__ void make_summary(const unsigned long long* keys, int qtail, Summary&
   out.size = o;
 }
 
+// ---------------------------------------------------------------------------------------------------
+// CTA-cooperative versions of the summary operations.  Every thread of the CTA calls them with the same
+// arguments; they end with a barrier.  Ranks are sums of unit weights, i.e. integers below 2^24 (the
+// caller falls back to the one-thread versions beyond that), so float rank arithmetic is exact and the
+// sequential pointer walks of SetPrune / SetCombine can be replaced by binary searches.
+struct CtaScratch {
+  int warp_tot[32];
+  int warp_tot2[32];
+  int total, total2;
+  int flag;
+};
+
+// exclusive scan of one int per thread over the CTA (blockDim.x == 1024); *total gets the CTA sum
+__device__ __forceinline__ int cta_excl_scan(int v, int* warp_tot, int* total) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  int inc = v;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) { int t = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += t; }
+  __syncthreads();   // protects warp_tot from the previous use
+  if (lane == 31) warp_tot[wid] = inc;
+  __syncthreads();
+  if (wid == 0) {
+    int t = warp_tot[lane];
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { int u = __shfl_up_sync(0xffffffffu, t, d); if (lane >= d) t += u; }
+    warp_tot[lane] = t;
+  }
+  __syncthreads();
+  const int base = wid ? warp_tot[wid - 1] : 0;
+  *total = warp_tot[31];
+  return base + inc - v;
+}
+
+__device__ void p_copy(float4* dst, const float4* src, int n) {
+  for (int i = threadIdx.x; i < n; i += blockDim.x) dst[i] = src[i];
+  __syncthreads();
+}
+
+// Queue::MakeSummary on sorted keys: one entry per distinct value, ranks from the weight prefix
+__device__ int p_make_summary(const unsigned long long* keys, int qtail, float4* out, CtaScratch& sc) {
+  const int per = (qtail + (int)blockDim.x - 1) / (int)blockDim.x;
+  const int lo = min(qtail, (int)threadIdx.x * per), hi = min(qtail, lo + per);
+  int starts = 0, wsum = 0;
+  for (int i = lo; i < hi; ++i) {
+    const unsigned long long k = keys[i];
+    const float v = unordered_bits((uint32_t)(k >> 32));
+    const bool st = i == 0 || !(unordered_bits((uint32_t)(keys[i - 1] >> 32)) == v);
+    starts += st;
+    wsum += (int)(uint32_t)k;
+  }
+  int tot_g, tot_w;
+  int g = cta_excl_scan(starts, sc.warp_tot, &tot_g);
+  int w = cta_excl_scan(wsum, sc.warp_tot2, &tot_w);
+  for (int i = lo; i < hi; ++i) {
+    const unsigned long long k = keys[i];
+    const float v = unordered_bits((uint32_t)(k >> 32));
+    const bool st = i == 0 || !(unordered_bits((uint32_t)(keys[i - 1] >> 32)) == v);
+    if (st) { out[g].x = (float)w; out[g].w = v; ++g; }
+    w += (int)(uint32_t)k;
+    const bool en = i == qtail - 1 || !(unordered_bits((uint32_t)(keys[i + 1] >> 32)) == v);
+    if (en) out[g - 1].y = (float)w;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < tot_g; i += blockDim.x) { float4 e = out[i]; e.z = __fsub_rn(e.y, e.x); out[i] = e; }
+  __syncthreads();
+  return tot_g;
+}
+
+// WQSummary::SetPrune.  For query k the sequential walk stops at the first i with dx2 < rmin[i+1] + rmax[i+1];
+// both dx2 (in k) and that sum (in i) are non-decreasing, so i(k) is an upper-bound search.
+__device__ int p_prune(float4* dst, const float4* src, int m, int maxsize, CtaScratch& sc) {
+  if (m <= maxsize) { p_copy(dst, src, m); return m; }
+  const float begin = src[0].y;
+  const float range = __fsub_rn(src[m - 1].x, src[0].y);
+  const int n = maxsize - 1;
+  const float fn = (float)n;
+  const int nq = n - 1;                                  // queries k = 1 .. n-1
+  const int per = (nq + (int)blockDim.x - 1) / (int)blockDim.x;
+  const int klo = 1 + min(nq, (int)threadIdx.x * per), khi = min(n, klo + per);
+  auto choose = [&](int k) -> int {                      // chosen source index, or -1 once the walk has hit the end
+    const float dx2 = __fmul_rn(2.0f, __fadd_rn(__fdiv_rn(__fmul_rn((float)k, range), fn), begin));
+    int lo = 2, hi = m;                                  // count j in [2, m-1] with rmin[j] + rmax[j] <= dx2
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      const float4 e = src[mid];
+      if (dx2 >= __fadd_rn(e.y, e.x)) lo = mid + 1; else hi = mid;
+    }
+    const int i = lo - 1;
+    if (i >= m - 1) return -1;
+    const float4 a = src[i], b = src[i + 1];
+    return dx2 < __fadd_rn(__fadd_rn(a.x, a.z), __fsub_rn(b.y, b.z)) ? i : i + 1;
+  };
+  int prev = klo > 1 && klo < n ? choose(klo - 1) : 0;   // lastidx seen by this thread's first query
+  int emits = 0;
+  for (int k = klo; k < khi; ++k) {
+    const int c = choose(k);
+    if (c < 0) break;
+    emits += (c != prev);
+    prev = c;
+  }
+  int total;
+  int pos = 1 + cta_excl_scan(emits, sc.warp_tot, &total);
+  prev = klo > 1 && klo < n ? choose(klo - 1) : 0;
+  int last_c = -2;                                       // chosen index of the last valid query in this range
+  for (int k = klo; k < khi; ++k) {
+    const int c = choose(k);
+    if (c < 0) break;
+    if (c != prev) dst[pos++] = src[c];
+    prev = c;
+    last_c = c;
+  }
+  if (threadIdx.x == 0) { dst[0] = src[0]; sc.flag = 0; }
+  __syncthreads();
+  if (last_c >= 0) atomicMax(&sc.flag, last_c);          // chosen indices never decrease: the max is the final lastidx
+  __syncthreads();
+  int size = 1 + total;
+  if (sc.flag != m - 1) { if (threadIdx.x == 0) dst[size] = src[m - 1]; ++size; }
+  __syncthreads();
+  return size;
+}
+
+__device__ __forceinline__ int lower_bound_value(const float4* s, int n, float v) {
+  int lo = 0, hi = n;
+  while (lo < hi) { const int mid = (lo + hi) >> 1; if (s[mid].w < v) lo = mid + 1; else hi = mid; }
+  return lo;
+}
+
+// WQSummary::SetCombine: a merge by value in which equal values fuse; every output entry depends only on its
+// own element and on its neighbours in the other list.  Returns the size, or -1 if FixError would have had to
+// change something (impossible with integer ranks; the caller then redoes the combine with one thread).
+__device__ int p_combine(float4* dst, const float4* A, int na, const float4* B, int nb, CtaScratch& sc) {
+  if (na == 0) { p_copy(dst, B, nb); return nb; }
+  if (nb == 0) { p_copy(dst, A, na); return na; }
+  const int T = (int)blockDim.x;
+  const int pa = (na + T - 1) / T, alo = min(na, (int)threadIdx.x * pa), ahi = min(na, alo + pa);
+  const int pb = (nb + T - 1) / T, blo = min(nb, (int)threadIdx.x * pb), bhi = min(nb, blo + pb);
+  int ea = 0, eb = 0;
+  for (int i = alo; i < ahi; ++i) { const float v = A[i].w; const int j = lower_bound_value(B, nb, v); ea += (j < nb && B[j].w == v); }
+  for (int j = blo; j < bhi; ++j) { const float v = B[j].w; const int i = lower_bound_value(A, na, v); eb += (i < na && A[i].w == v); }
+  int tot_a, tot_b;
+  int Ea = cta_excl_scan(ea, sc.warp_tot, &tot_a);
+  int Eb = cta_excl_scan(eb, sc.warp_tot2, &tot_b);
+  const float armax = A[na - 1].y, brmax = B[nb - 1].y;
+  for (int i = alo; i < ahi; ++i) {
+    const float4 a = A[i];
+    const int j = lower_bound_value(B, nb, a.w);
+    const bool eq = j < nb && B[j].w == a.w;
+    float4 r;
+    if (eq) {
+      const float4 b = B[j];
+      r = make_float4(__fadd_rn(a.x, b.x), __fadd_rn(a.y, b.y), __fadd_rn(a.z, b.z), a.w);
+    } else {
+      const float bprev = j > 0 ? __fadd_rn(B[j - 1].x, B[j - 1].z) : 0.f;               // RMinNext of the last smaller b
+      const float bnext = j < nb ? __fsub_rn(B[j].y, B[j].z) : brmax;                     // RMaxPrev of the next b, or b's last rmax
+      r = make_float4(__fadd_rn(a.x, bprev), __fadd_rn(a.y, bnext), a.z, a.w);
+    }
+    dst[i + j - Ea] = r;
+    Ea += eq;
+  }
+  for (int j = blo; j < bhi; ++j) {
+    const float4 b = B[j];
+    const int i = lower_bound_value(A, na, b.w);
+    const bool eq = i < na && A[i].w == b.w;
+    if (!eq) {
+      const float aprev = i > 0 ? __fadd_rn(A[i - 1].x, A[i - 1].z) : 0.f;
+      const float anext = i < na ? __fsub_rn(A[i].y, A[i].z) : armax;
+      dst[j + i - Eb] = make_float4(__fadd_rn(b.x, aprev), __fadd_rn(b.y, anext), b.z, b.w);
+    }
+    Eb += eq;
+  }
+  if (threadIdx.x == 0) sc.flag = 0;
+  __syncthreads();
+  const int size = na + nb - tot_a;
+  int bad = 0;                                                                            // FixError would act iff one of these holds
+  for (int i = threadIdx.x; i < size; i += T) {
+    const float4 e = dst[i];
+    if (e.y < __fadd_rn(e.x, e.z)) bad = 1;
+    if (i > 0) { const float4 p = dst[i - 1]; if (e.x < p.x || e.y < p.y) bad = 1; }
+  }
+  if (bad) sc.flag = 1;
+  __syncthreads();
+  const int res = sc.flag ? -1 : size;
+  __syncthreads();
+  return res;
+}
+
 __device__ __forceinline__ int next_pow2(int v) { int p = 2; while (p < v) p <<= 1; return p; }
 
 __global__ void __launch_bounds__(kSketchThreads)
@@ -181,6 +367,8 @@ k_sketch_cuts(const float* __restrict__ X, long long ldx, int f, int nfold,
   __shared__ int warp_tot[kSketchThreads / 32];
   __shared__ int level_size[40];
   __shared__ int levels_in_use;
+  __shared__ CtaScratch sc;
+  const bool parallel_ok = n < (1ll << 24);   // ranks stay exact integers in fp32
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
 
   if (tid == 0) { levels_in_use = 0; for (int l = 0; l < 40; ++l) level_size[l] = 0; }
@@ -233,7 +421,39 @@ k_sketch_cuts(const float* __restrict__ X, long long ldx, int f, int nfold,
       for (int t = qcap + tid; t < n2; t += blockDim.x) keys[t] = ~0ull;
       __syncthreads();
       cta_sort(keys, n2);
-      if (tid == 0) {
+      if (parallel_ok) {
+        temp.size = p_make_summary(keys, qcap, temp.d, sc);
+        for (int l = 1;; ++l) {   // QuantileSketchTemplate::PushTemp, all threads in step
+          if (tid == 0 && l + 1 > levels_in_use) levels_in_use = l + 1;
+          float4* lvd = level_space + (size_t)l * L;
+          const int lsz = level_size[l];
+          __syncthreads();
+          if (lsz == 0) {
+            const int sz = p_prune(lvd, temp.d, temp.size, L, sc);
+            if (tid == 0) level_size[l] = sz;
+            __syncthreads();
+            break;
+          }
+          const int l0sz = p_prune(level_space, temp.d, temp.size, L, sc);
+          int csz = p_combine(temp.d, level_space, l0sz, lvd, lsz, sc);
+          if (csz < 0) {   // never with integer ranks; keep the reference behaviour anyway
+            if (tid == 0) { Summary a0 = { level_space, l0sz }, b0 = { lvd, lsz }; s_combine(temp, a0, b0); sc.total = temp.size; }
+            __syncthreads();
+            csz = sc.total;
+            __syncthreads();
+          }
+          temp.size = csz;
+          if (csz > L) {
+            if (tid == 0) level_size[l] = 0;
+            __syncthreads();
+          } else {
+            p_copy(lvd, temp.d, csz);
+            if (tid == 0) level_size[l] = csz;
+            __syncthreads();
+            break;
+          }
+        }
+      } else if (tid == 0) {
         make_summary(keys, qcap, temp);
         for (int l = 1;; ++l) {   // QuantileSketchTemplate::PushTemp
           if (l + 1 > levels_in_use) levels_in_use = l + 1;
@@ -267,7 +487,44 @@ k_sketch_cuts(const float* __restrict__ X, long long ldx, int f, int nfold,
   for (int t = qtail + tid; t < n2; t += blockDim.x) keys[t] = ~0ull;
   __syncthreads();
   cta_sort(keys, n2);
+  if (parallel_ok) {
+    out.size = p_make_summary(keys, qtail, out.d, sc);
+    const int used = levels_in_use;
+    __syncthreads();
+    if (used != 0) {
+      int l0sz = p_prune(level_space, out.d, out.size, L, sc);
+      for (int l = 1; l < used; ++l) {
+        const int lsz = level_size[l];
+        if (lsz == 0) continue;
+        float4* lvd = level_space + (size_t)l * L;
+        if (l0sz == 0) {
+          p_copy(level_space, lvd, lsz);
+          l0sz = lsz;
+        } else {
+          int csz = p_combine(out.d, level_space, l0sz, lvd, lsz, sc);
+          if (csz < 0) {
+            if (tid == 0) { Summary a0 = { level_space, l0sz }, b0 = { lvd, lsz }; s_combine(out, a0, b0); sc.total = out.size; }
+            __syncthreads();
+            csz = sc.total;
+            __syncthreads();
+          }
+          l0sz = p_prune(level_space, out.d, csz, L, sc);
+        }
+      }
+      p_copy(out.d, level_space, l0sz);
+      out.size = l0sz;
+    } else if (out.size > L) {
+      const int sz = p_prune(temp.d, out.d, out.size, L, sc);
+      p_copy(out.d, temp.d, sz);
+      out.size = sz;
+    }
+    const long long inter_p = n < (long long)kBins * 8 ? n : (long long)kBins * 8;
+    red.size = p_prune(red.d, out.d, out.size, (int)inter_p, sc);
+    const int mnb = inter_p < kBins ? (int)inter_p : kBins;
+    temp.size = p_prune(temp.d, red.d, red.size, mnb + 1, sc);
+  }
   if (tid == 0) {
+    if (!parallel_ok) {
     make_summary(keys, qtail, out);
     Summary l0 = { level_space, 0 };
     if (levels_in_use != 0) {
@@ -287,10 +544,13 @@ k_sketch_cuts(const float* __restrict__ X, long long ldx, int f, int nfold,
       s_prune(temp, out, L);
       s_copy(out, temp);
     }
+    }
     const long long inter = n < (long long)kBins * 8 ? n : (long long)kBins * 8;
-    s_prune(red, out, (int)inter);
     const int max_num_bins = inter < kBins ? (int)inter : kBins;
-    s_prune(temp, red, max_num_bins + 1);
+    if (!parallel_ok) {
+      s_prune(red, out, (int)inter);
+      s_prune(temp, red, max_num_bins + 1);
+    }
     // hist_util.h AddCutPoint + the trailing sentinel of MakeCuts
     const int required = temp.size < max_num_bins ? temp.size : max_num_bins;
     int nc = 0;

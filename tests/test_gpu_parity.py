@@ -97,6 +97,24 @@ def test_cuts_and_bins_bit_exact_multilevel_sketch(synth_pair):
     assert np.array_equal(eng.bins(4, 1), ctx.all_bins(1))
 
 
+def test_cuts_bit_exact_deep_summary_hierarchy():
+    """1M train rows per fold: limit_size 14337, 35 queue flushes per stream, merges cascading through seven
+    summary levels (the shape of the 1M x 50 benchmark's streams), incl. a low-cardinality and a skewed column."""
+    from gentun_b200.engine import Engine
+    x, y = make_dataset(2000000, 10, seed=1005)
+    x = np.ascontiguousarray(x[:, [0, 3, 8, 9]])
+    eng = Engine(x, y)
+    ctx = orc.Context(x, y, 2)
+    for k in range(2):
+        cu, nc = eng.cuts(2, k)
+        ocu, onc = ctx.cuts(k)
+        assert np.array_equal(nc, onc)
+        for j in range(4):
+            assert np.array_equal(cu[j, :nc[j]].view(np.uint32), ocu[j, :nc[j]].view(np.uint32)), (k, j)
+    eng.close()
+    ctx.close()
+
+
 def test_ragged_and_tiny_inputs():
     from gentun_b200.engine import Engine
     for n, f, nfold in [(53, 3, 5), (1001, 33, 3), (257, 1, 2)]:
@@ -226,6 +244,25 @@ def test_regression_parity_synthetic_deep(synth_pair):
     for i, g in enumerate(gs):
         want = ctx.cv(g, orc.make_opts(nfold=4, num_boost_round=12))
         assert rel(fit[i], want["fitness"]) < REL_TOL, (i, fit[i], want["fitness"])
+
+
+@pytest.mark.parametrize("f", [70, 100, 200])
+def test_wide_feature_matrices_parity(f):
+    """More than two 32-feature groups: several histogram CTAs per work item (70 -> three single-group CTAs,
+    100 -> two group-pair CTAs, 200 -> seven), both histogram cell formats, masked features."""
+    from gentun_b200.engine import Engine
+    x, y = make_dataset(24000, f, seed=2000 + f)
+    eng = Engine(x, y)
+    ctx = orc.Context(x, y, 3)
+    gs = [genes(max_depth=9, min_child_weight=0, eta=0.2), genes(max_depth=4, colsample_bytree=0.6, colsample_bylevel=0.8)]
+    a, _ = eng.evaluate(gs, nfold=3, num_boost_round=6)
+    b, _ = eng.evaluate(gs, nfold=3, num_boost_round=6)
+    assert np.array_equal(a, b)
+    for i, g in enumerate(gs):
+        want = ctx.cv(g, orc.make_opts(nfold=3, num_boost_round=6))
+        assert rel(a[i], want["fitness"]) < REL_TOL, (f, i, a[i], want["fitness"])
+    eng.close()
+    ctx.close()
 
 
 def test_logistic_logloss_parity():
