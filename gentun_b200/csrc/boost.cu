@@ -57,13 +57,19 @@ __device__ __forceinline__ float split_gain(const JobParams& p, double GL, doubl
 // fp32 estimate of split_gain - root_gain's first two terms (same formulas, float throughout);
 // mag returns the size of the terms, from which the caller bounds the estimate's rounding error
 __device__ __forceinline__ float gain_term_est(const JobParams& p, float G, float H) {
-  if (H <= 0.f) return 0.f;   // callers pass only candidates whose children already satisfy min_child_weight
-  const float t = G > p.alpha ? G - p.alpha : (G < -p.alpha ? G + p.alpha : 0.f);
+  // branch-free (lanes of a warp scan different features, so data-dependent branches would serialise):
+  // ThresholdL1 as G - clamp(G, -alpha, alpha); an empty side (H <= 0) contributes nothing
+  const float t = G - fminf(fmaxf(G, -p.alpha), p.alpha);
   const float d = H + p.lambda;
-  if (p.mds == 0.0f) return __fdividef(t * t, d);
-  float w = -__fdividef(t, d);
-  if (fabsf(w) > p.mds) w = copysignf(p.mds, w);
-  return -(2.0f * G * w + d * (w * w));
+  float r;
+  if (p.mds == 0.0f) {                 // uniform across the CTA
+    r = __fdividef(t * t, d);
+  } else {
+    float w = -__fdividef(t, d);
+    w = fminf(fmaxf(w, -p.mds), p.mds);
+    r = -(2.0f * G * w + d * (w * w));
+  }
+  return H > 0.f ? r : 0.f;
 }
 __device__ __forceinline__ float split_gain_est(const JobParams& p, float GL, float HL, float GR, float HR, float& mag) {
   const float a = gain_term_est(p, GL, HL), b = gain_term_est(p, GR, HR);
@@ -433,16 +439,22 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 3 : 1) k_
   const HistItem it = w.hitems[(size_t)j * w.hist_cap + item_idx];
   extern __shared__ int sh[];   // [group in CTA][g plane | h plane][bin][feature lane]
   __shared__ unsigned s_abs[2];  // sum |g_q| and sum h_q since the last flush, in units of 64
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  // row ids of the first two iterations are requested before the shared histogram is cleared, so that the
+  // clear overlaps the first of the three dependent loads (item -> row id -> bin line)
+  const uint32_t* ridx = w.ridx + ((size_t)j * 2 + (size_t)((it.flags >> 1) & 1)) * w.nt_stride + it.begin;
+  const uint32_t cnt = it.cnt;
+  const uint32_t my0 = (uint32_t)wid * 32u + (uint32_t)lane;
+  uint32_t row_b = my0 < cnt ? ridx[my0] : 0xffffffffu;                              // iteration 0
+  uint32_t row_c = my0 + kStride < cnt ? ridx[my0 + kStride] : 0xffffffffu;          // iteration 1
   for (int i = threadIdx.x; i < kGroupsPerCta * 2 * kBins * kLanes / 4; i += kThreads) reinterpret_cast<int4*>(sh)[i] = make_int4(0, 0, 0, 0);
   if (threadIdx.x < 2) s_abs[threadIdx.x] = 0u;
   __syncthreads();
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int rslot = lane / UNITS, unit = lane % UNITS;
   const int rot = UNITS == 2 ? rslot : rslot * 2 + (unit >> 1);   // 16 distinct rotations per bank half
   const bool q1 = (rot >> 2) & 1, q2 = (rot >> 3) & 1;
   const int rb = (rot & 3) * 8;
   const uint8_t* bins_unit = w.folds[jp.fold].bins + (size_t)cg * kGroupsPerCta * kLanes + unit * 16;
-  const uint32_t* ridx = w.ridx + ((size_t)j * 2 + (size_t)((it.flags >> 1) & 1)) * w.nt_stride + it.begin;
   const int2* gq = w.gq + (size_t)j * w.nt_stride;
   const int fpad = w.fpad;
   const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(sh);
@@ -454,11 +466,7 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 3 : 1) k_
     asm volatile("mov.u32 %0, %1;" : "=r"(cs[s]) : "r"(v));   // opaque: keep it in a register, never rematerialise
   }
   const bool atomic_flush = it.flags & 1;
-  const uint32_t cnt = it.cnt;
   // three-deep software pipeline: row ids two iterations ahead, bin bytes + gradients one ahead
-  const uint32_t my0 = (uint32_t)wid * 32u + (uint32_t)lane;
-  uint32_t row_b = my0 < cnt ? ridx[my0] : 0xffffffffu;                              // iteration 0
-  uint32_t row_c = my0 + kStride < cnt ? ridx[my0 + kStride] : 0xffffffffu;          // iteration 1
   HistStage<UNITS> cur, nxt;
   hist_load<UNITS>(cur, row_b, rslot, bins_unit, gq, fpad);
   row_b = row_c;
@@ -497,11 +505,6 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 3 : 1) k_
 }
 
 // ------------------------------------------------------------------ X6: split enumeration
-// One CTA per (job, parent).  Warps = 2 children x feature groups x bin chunks, lane = feature.
-// Pass 1: every warp sums its chunk of bins (forming the sibling histogram on the fly as
-// parent - built and storing it when a later level needs it as a parent).  Pass 2: with the chunk
-// prefix from shared memory each lane runs EnumerateSplit<+1> over its bins; candidates are merged
-// with warp shuffles, then across warps.
 struct Cand { float chg; int f; int b; long long GL, HL; };
 
 __device__ __forceinline__ bool better(float chg, int f, int b, float ochg, int of, int ob) {
@@ -515,7 +518,53 @@ __device__ __forceinline__ bool better(float chg, int f, int b, float ochg, int 
 
 __host__ __device__ inline int scan_chunks(int groups) { return groups <= 2 ? 8 : groups <= 4 ? 4 : 2; }
 
-__global__ void __launch_bounds__(1024) k_scan(Wave w, int level) {
+// Per-lane state of one child while its feature's bins are scanned.
+struct ChildScan {
+  long long Gt, Ht;        // node totals
+  float Gt_f, Ht_f;        // same, scaled, fp32
+  float root_gain;
+  long long GL, HL;        // running prefix
+  float e1, e2;            // best and second-best estimate of this lane
+  int b1;
+  long long GL1, HL1;      // prefix at the best estimate
+  float smax;
+};
+
+__device__ __forceinline__ void child_step(ChildScan& c, const JobParams& jp, const longlong2 e, int b, bool in_range,
+                                           long long hmin_q, float isg, float ish) {
+  c.GL += e.x; c.HL += e.y;
+  // every bin is estimated and then masked: no divergent control flow in the hot loop
+  const bool cand = in_range & ((e.x | e.y) != 0) & (c.HL >= hmin_q) & ((c.Ht - c.HL) >= hmin_q);
+  float mag;
+  const float gl = (float)c.GL * isg, hl = (float)c.HL * ish;
+  float est = split_gain_est(jp, gl, hl, c.Gt_f - gl, c.Ht_f - hl, mag);
+  est = cand ? est : -3.0e38f;
+  c.smax = fmaxf(c.smax, cand ? mag : 0.0f);
+  const bool top = est > c.e1;
+  c.e2 = fmaxf(c.e2, fminf(c.e1, est));
+  c.e1 = fmaxf(c.e1, est);
+  c.b1 = top ? b : c.b1;
+  c.GL1 = top ? c.GL : c.GL1;
+  c.HL1 = top ? c.HL : c.HL1;
+}
+
+__device__ __forceinline__ void exact_candidate(Cand& best, const JobParams& jp, const ChildScan& c, long long GL, long long HL, int f, int b,
+                                                double inv_sg, double inv_sh) {
+  const double gl = (double)GL * inv_sg, hl = (double)HL * inv_sh;
+  const double gr = (double)(c.Gt - GL) * inv_sg, hr = (double)(c.Ht - HL) * inv_sh;
+  if (hl >= jp.mcw && hr >= jp.mcw) {
+    const float chg = split_gain(jp, gl, hl, gr, hr) - c.root_gain;
+    if (!isinf(chg) && chg > best.chg) { best.chg = chg; best.f = f; best.b = b; best.GL = GL; best.HL = HL; }
+  }
+}
+
+// One CTA per (job, parent).  Warps = feature groups x bin chunks, lane = feature; every warp scans BOTH
+// children of the parent: the built child's cells are read once, the sibling's are formed on the fly as
+// parent - built (and stored when a later level needs them as a parent).
+// Pass 1: chunk sums.  Pass 2: with the chunk prefix from shared memory each lane runs EnumerateSplit<+1>
+// over its bins with a branch-free fp32 gain estimate; only candidates within the estimate's error
+// margin of the best one are re-evaluated in the reference's double/float expression order.
+__global__ void __launch_bounds__(512, 2) k_scan(Wave w, int level) {
   const int j = blockIdx.y;
   const JobState& js = w.js[j];
   if ((int)blockIdx.x >= js.n_pairs) return;
@@ -523,148 +572,144 @@ __global__ void __launch_bounds__(1024) k_scan(Wave w, int level) {
   const PairRec pr = w.pairs[(size_t)j * w.pair_cap + blockIdx.x];
   const int G = w.groups, NCH = scan_chunks(G), CB = kBins / NCH;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int c = warp / (G * NCH), grp = (warp % (G * NCH)) / NCH, ch = warp % NCH;
+  const int grp = warp / NCH, ch = warp % NCH;
   Node* nodes = w.nodes + (size_t)j * kNodeCap;
   TreeNode* tree = w.tree + (size_t)j * kNodeCap;
-  const bool live = (level > 0) || (c == 0);
-  const int node = level == 0 ? 0 : 2 * pr.parent + 1 + c;
-  const bool is_built = (level == 0) || (c == pr.build_right);
-  const int built_node = level == 0 ? 0 : 2 * pr.parent + 1 + pr.build_right;
+  const bool has_sib = level > 0;
+  const int bnode = level == 0 ? 0 : 2 * pr.parent + 1 + pr.build_right;       // histogram built by k_hist
+  const int snode = level == 0 ? 0 : 2 * pr.parent + 2 - pr.build_right;       // its sibling
   const FoldDev& fd = w.folds[jp.fold];
   const int f = grp * kLanes + lane;
   const int nc = f < w.f ? fd.ncuts[f] : 0;
   const bool factive = f < w.f && ((js.lmask[f >> 5] >> (f & 31)) & 1u);
   const int maxnc = w.grp_maxnc[jp.fold * G + grp];
-  const bool write_sib = live && !is_built && (level + 1 < jp.max_depth);
+  const bool write_sib = has_sib && (level + 1 < jp.max_depth);
   const size_t goff = (size_t)grp * (kBins * kLanes) + lane;
-  const HistEntry* hbuilt = node_hist(w, jp, level, built_node);
-  const HistEntry* hpar = level > 0 ? node_hist(w, jp, level - 1, pr.parent) : nullptr;
-  HistEntry* hown = node_hist(w, jp, level, node);
-  const bool nar_b = node_narrow(nodes[built_node].cnt), nar_o = node_narrow(nodes[node].cnt);
-  const bool nar_p = level > 0 ? node_narrow(nodes[pr.parent].cnt) : false;
-  const long long Gt = nodes[node].G, Ht = nodes[node].H;
+  const HistEntry* hbuilt = node_hist(w, jp, level, bnode);
+  const HistEntry* hpar = has_sib ? node_hist(w, jp, level - 1, pr.parent) : nullptr;
+  HistEntry* hsib = node_hist(w, jp, level, snode);
+  const bool nar_b = node_narrow(nodes[bnode].cnt), nar_s = node_narrow(nodes[snode].cnt);
+  const bool nar_p = has_sib ? node_narrow(nodes[pr.parent].cnt) : false;
   const double inv_sg = js.inv_sg, inv_sh = js.inv_sh;
-  float root_gain = nodes[node].root_gain;
-  if (level == 0) root_gain = calc_gain(jp, (double)Gt * inv_sg, (double)Ht * inv_sh);
+  const float isg = (float)inv_sg, ish = (float)inv_sh;
   const int b_lo = ch * CB, b_hi = min(b_lo + CB, maxnc);
 
-  __shared__ longlong2 s_sum[32][kLanes];   // chunk sums per warp
-  __shared__ Cand s_c[32];
-  longlong2 acc = make_longlong2(0, 0);
-  if (live) {
+  ChildScan cb, cs;   // built child, sibling
+  cb.Gt = nodes[bnode].G; cb.Ht = nodes[bnode].H; cb.root_gain = nodes[bnode].root_gain;
+  cs.Gt = nodes[snode].G; cs.Ht = nodes[snode].H; cs.root_gain = nodes[snode].root_gain;
+  if (level == 0) cb.root_gain = calc_gain(jp, (double)cb.Gt * inv_sg, (double)cb.Ht * inv_sh);
+  cb.Gt_f = (float)cb.Gt * isg; cb.Ht_f = (float)cb.Ht * ish;
+  cs.Gt_f = (float)cs.Gt * isg; cs.Ht_f = (float)cs.Ht * ish;
+
+  __shared__ longlong2 s_sum[16][2][kLanes];   // chunk sums per warp: built, sibling
+  __shared__ float s_est[16][4];
+  __shared__ Cand s_c[16][2];
+  {
+    longlong2 ab = make_longlong2(0, 0), as = make_longlong2(0, 0);
 #pragma unroll 4
     for (int b = b_lo; b < b_hi; ++b) {
-      longlong2 e = load_cell(hbuilt, nar_b, goff + (size_t)b * kLanes);
-      if (!is_built) {
+      const longlong2 eb = load_cell(hbuilt, nar_b, goff + (size_t)b * kLanes);
+      ab.x += eb.x; ab.y += eb.y;
+      if (has_sib) {
         const longlong2 pe = load_cell(hpar, nar_p, goff + (size_t)b * kLanes);
-        e.x = pe.x - e.x; e.y = pe.y - e.y;
-        if (write_sib) store_cell(hown, nar_o, goff + (size_t)b * kLanes, e);
+        const longlong2 es = make_longlong2(pe.x - eb.x, pe.y - eb.y);
+        if (write_sib) store_cell(hsib, nar_s, goff + (size_t)b * kLanes, es);
+        as.x += es.x; as.y += es.y;
       }
-      acc.x += e.x; acc.y += e.y;
     }
+    s_sum[warp][0][lane] = ab;
+    s_sum[warp][1][lane] = as;
   }
-  s_sum[warp][lane] = acc;
   __syncthreads();
-  // Pass 2a: a cheap fp32 estimate of every candidate's gain.  Only candidates whose estimate is within
-  // the estimate's error margin of the best one can be the exact argmax; pass 2b re-evaluates just those
-  // in the reference's double/float expression order.  (FP64 evaluation of all candidates made this
-  // kernel compute-bound at the deep levels.)
-  const long long hmin_q = (long long)ceil((double)jp.mcw * (double)js.sh);   // hl >= mcw  <=>  HL_q >= mcw * sh (exact)
-  long long GL0 = 0, HL0 = 0;
-  if (live && factive)
-    for (int k = 0; k < ch; ++k) { const longlong2 t = s_sum[warp - ch + k][lane]; GL0 += t.x; HL0 += t.y; }
-  const int hi = (live && factive) ? min(b_hi, nc) : b_lo;
-  const float isg = (float)inv_sg, ish = (float)inv_sh;
-  const float Gt_f = (float)Gt * isg, Ht_f = (float)Ht * ish;
-  float amax = -3.0e38f, smax = 0.0f;
-  float e1 = -3.0e38f, e2 = -3.0e38f;   // this lane's best and second-best estimate
-  int b1 = -1;
-  long long GL1 = 0, HL1 = 0;
-  {
-    long long GL = GL0, HL = HL0;
-    for (int b = b_lo; b < hi; ++b) {
-      longlong2 e = load_cell(hbuilt, nar_b, goff + (size_t)b * kLanes);
-      if (!is_built) { const longlong2 pe = load_cell(hpar, nar_p, goff + (size_t)b * kLanes); e.x = pe.x - e.x; e.y = pe.y - e.y; }
-      GL += e.x; HL += e.y;
-      if ((e.x != 0 || e.y != 0) && HL >= hmin_q && (Ht - HL) >= hmin_q) {
-        float mag;
-        const float gl = (float)GL * isg, hl = (float)HL * ish;
-        const float est = split_gain_est(jp, gl, hl, Gt_f - gl, Ht_f - hl, mag);
-        smax = fmaxf(smax, mag);
-        if (est > e1) { e2 = e1; e1 = est; b1 = b; GL1 = GL; HL1 = HL; }
-        else if (est > e2) e2 = est;
-      }
-    }
-    amax = e1;
+  cb.GL = 0; cb.HL = 0; cs.GL = 0; cs.HL = 0;
+  for (int k = 0; k < ch; ++k) {
+    const longlong2 tb = s_sum[warp - ch + k][0][lane], ts = s_sum[warp - ch + k][1][lane];
+    cb.GL += tb.x; cb.HL += tb.y; cs.GL += ts.x; cs.HL += ts.y;
   }
+  const long long GLb0 = cb.GL, HLb0 = cb.HL, GLs0 = cs.GL, HLs0 = cs.HL;
+  // hl >= mcw  <=>  HL_q >= mcw * sh (exact: sh is a power of two)
+  const long long hmin_q = (long long)ceil((double)jp.mcw * (double)js.sh);
+  cb.e1 = cb.e2 = cs.e1 = cs.e2 = -3.0e38f; cb.b1 = cs.b1 = -1; cb.GL1 = cb.HL1 = cs.GL1 = cs.HL1 = 0; cb.smax = cs.smax = 0.f;
+  const int hi = factive ? min(b_hi, nc) : b_lo;
+  for (int b = b_lo; b < hi; ++b) {
+    const longlong2 eb = load_cell(hbuilt, nar_b, goff + (size_t)b * kLanes);
+    child_step(cb, jp, eb, b, true, hmin_q, isg, ish);
+    if (has_sib) {
+      const longlong2 pe = load_cell(hpar, nar_p, goff + (size_t)b * kLanes);
+      child_step(cs, jp, make_longlong2(pe.x - eb.x, pe.y - eb.y), b, true, hmin_q, isg, ish);
+    }
+  }
+  float v0 = cb.e1, v1 = cb.smax, v2 = cs.e1, v3 = cs.smax;
   for (int d = 16; d; d >>= 1) {
-    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, d));
-    smax = fmaxf(smax, __shfl_xor_sync(0xffffffffu, smax, d));
+    v0 = fmaxf(v0, __shfl_xor_sync(0xffffffffu, v0, d)); v1 = fmaxf(v1, __shfl_xor_sync(0xffffffffu, v1, d));
+    v2 = fmaxf(v2, __shfl_xor_sync(0xffffffffu, v2, d)); v3 = fmaxf(v3, __shfl_xor_sync(0xffffffffu, v3, d));
   }
-  __shared__ float s_est[32][2];
-  if (lane == 0) { s_est[warp][0] = amax; s_est[warp][1] = smax; }
+  if (lane == 0) { s_est[warp][0] = v0; s_est[warp][1] = v1; s_est[warp][2] = v2; s_est[warp][3] = v3; }
   __syncthreads();
-  {
-    const int w0 = c * G * NCH;
-    amax = -3.0e38f; smax = 0.0f;
-    for (int k = 0; k < G * NCH; ++k) { amax = fmaxf(amax, s_est[w0 + k][0]); smax = fmaxf(smax, s_est[w0 + k][1]); }
+  v0 = v2 = -3.0e38f; v1 = v3 = 0.f;
+  for (int k = 0; k < G * NCH; ++k) {
+    v0 = fmaxf(v0, s_est[k][0]); v1 = fmaxf(v1, s_est[k][1]); v2 = fmaxf(v2, s_est[k][2]); v3 = fmaxf(v3, s_est[k][3]);
   }
-  // estimate error: a few fp32 roundings on terms of size <= smax (the right-hand sums are formed by an
-  // fp32 subtraction from the node totals), plus the root gain
-  const float margin = 3.2e-5f * (smax + fabsf(root_gain)) + 1e-12f;
-  // a candidate can win only with est close to the best estimate and with a positive gain (est > root gain)
-  const float cut = fmaxf(amax, root_gain) - 2.0f * margin;
-  Cand best{0.0f, -1, -1, 0, 0};
-  if (e1 >= cut) {
-    if (e2 < cut) {
-      // the usual case: one candidate of this lane survives; evaluate it exactly from the saved prefix
-      const double gl = (double)GL1 * inv_sg, hl = (double)HL1 * inv_sh;
-      const double gr = (double)(Gt - GL1) * inv_sg, hr = (double)(Ht - HL1) * inv_sh;
-      if (hl >= jp.mcw && hr >= jp.mcw) {
-        const float chg = split_gain(jp, gl, hl, gr, hr) - root_gain;
-        if (!isinf(chg) && chg > best.chg) { best.chg = chg; best.f = f; best.b = b1; best.GL = GL1; best.HL = HL1; }
-      }
-    } else {
-      // several near-ties in this lane: walk the bins again in scan order
-      long long GL = GL0, HL = HL0;
-      for (int b = b_lo; b < hi; ++b) {
-        longlong2 e = load_cell(hbuilt, nar_b, goff + (size_t)b * kLanes);
-        if (!is_built) { const longlong2 pe = load_cell(hpar, nar_p, goff + (size_t)b * kLanes); e.x = pe.x - e.x; e.y = pe.y - e.y; }
-        GL += e.x; HL += e.y;
-        if ((e.x != 0 || e.y != 0) && HL >= hmin_q && (Ht - HL) >= hmin_q) {   // an empty bin repeats the previous candidate (strict >)
-          float mag;
-          const float glf = (float)GL * isg, hlf = (float)HL * ish;
-          const float est = split_gain_est(jp, glf, hlf, Gt_f - glf, Ht_f - hlf, mag);
-          if (est >= cut) {
-            const double gl = (double)GL * inv_sg, hl = (double)HL * inv_sh;
-            const double gr = (double)(Gt - GL) * inv_sg, hr = (double)(Ht - HL) * inv_sh;
-            if (hl >= jp.mcw && hr >= jp.mcw) {
-              const float chg = split_gain(jp, gl, hl, gr, hr) - root_gain;
-              if (!isinf(chg) && chg > best.chg) { best.chg = chg; best.f = f; best.b = b; best.GL = GL; best.HL = HL; }
+  Cand bestc[2];
+#pragma unroll
+  for (int side = 0; side < 2; ++side) {
+    const ChildScan& c = side == 0 ? cb : cs;
+    const float amax = side == 0 ? v0 : v2, smax = side == 0 ? v1 : v3;
+    Cand best{0.0f, -1, -1, 0, 0};
+    if (side == 0 || has_sib) {
+      // estimate error: a few fp32 roundings on terms of size <= smax (the right-hand sums come from an fp32
+      // subtraction from the node totals), plus the root gain
+      const float margin = 3.2e-5f * (smax + fabsf(c.root_gain)) + 1e-12f;
+      // a candidate can win only with est close to the best estimate and with a positive gain (est > root gain)
+      const float cut = fmaxf(amax, c.root_gain) - 2.0f * margin;
+      if (c.e1 >= cut) {
+        if (c.e2 < cut) {
+          // the usual case: one candidate of this lane survives; evaluate it exactly from the saved prefix
+          exact_candidate(best, jp, c, c.GL1, c.HL1, f, c.b1, inv_sg, inv_sh);
+        } else {
+          // several near-ties in this lane: walk the bins again in scan order (an empty bin repeats the previous
+          // candidate, which never wins under strict >)
+          long long GL = side == 0 ? GLb0 : GLs0, HL = side == 0 ? HLb0 : HLs0;
+          for (int b = b_lo; b < hi; ++b) {
+            longlong2 e = load_cell(hbuilt, nar_b, goff + (size_t)b * kLanes);
+            if (side == 1) { const longlong2 pe = load_cell(hpar, nar_p, goff + (size_t)b * kLanes); e.x = pe.x - e.x; e.y = pe.y - e.y; }
+            GL += e.x; HL += e.y;
+            if ((e.x != 0 || e.y != 0) && HL >= hmin_q && (c.Ht - HL) >= hmin_q) {
+              float mag;
+              const float glf = (float)GL * isg, hlf = (float)HL * ish;
+              const float est = split_gain_est(jp, glf, hlf, c.Gt_f - glf, c.Ht_f - hlf, mag);
+              if (est >= cut) exact_candidate(best, jp, c, GL, HL, f, b, inv_sg, inv_sh);
             }
           }
         }
       }
     }
+    for (int d = 16; d; d >>= 1) {
+      const float ochg = __shfl_xor_sync(0xffffffffu, best.chg, d);
+      const int of = __shfl_xor_sync(0xffffffffu, best.f, d);
+      const int ob = __shfl_xor_sync(0xffffffffu, best.b, d);
+      const long long oGL = __shfl_xor_sync(0xffffffffu, best.GL, d);
+      const long long oHL = __shfl_xor_sync(0xffffffffu, best.HL, d);
+      if (better(ochg, of, ob, best.chg, best.f, best.b)) { best.chg = ochg; best.f = of; best.b = ob; best.GL = oGL; best.HL = oHL; }
+    }
+    bestc[side] = best;
   }
-  for (int d = 16; d; d >>= 1) {
-    const float ochg = __shfl_xor_sync(0xffffffffu, best.chg, d);
-    const int of = __shfl_xor_sync(0xffffffffu, best.f, d);
-    const int ob = __shfl_xor_sync(0xffffffffu, best.b, d);
-    const long long oGL = __shfl_xor_sync(0xffffffffu, best.GL, d);
-    const long long oHL = __shfl_xor_sync(0xffffffffu, best.HL, d);
-    if (better(ochg, of, ob, best.chg, best.f, best.b)) { best.chg = ochg; best.f = of; best.b = ob; best.GL = oGL; best.HL = oHL; }
-  }
-  if (lane == 0) s_c[warp] = best;
+  if (lane == 0) { s_c[warp][0] = bestc[0]; s_c[warp][1] = bestc[1]; }
   __syncthreads();
-  if (!(lane == 0 && grp == 0 && ch == 0 && live)) return;
+  // one thread per child finishes the node: thread 0 the built child, thread 32 the sibling
+  const int side = warp;
+  if (lane != 0 || side > 1 || (side == 1 && !has_sib)) return;
+  Cand best = s_c[0][side];
   for (int k = 1; k < G * NCH; ++k) {
-    const Cand o = s_c[warp + k];
+    const Cand o = s_c[k][side];
     if (better(o.chg, o.f, o.b, best.chg, best.f, best.b)) best = o;
   }
+  const ChildScan& c = side == 0 ? cb : cs;
+  const int node = side == 0 ? bnode : snode;
+  const long long Gt = c.Gt, Ht = c.Ht;
   Node& nd = nodes[node];
   if (level == 0) {
-    nd.root_gain = root_gain;
+    nd.root_gain = c.root_gain;
     nd.leaf = jp.eta * calc_weight(jp, (double)Gt * inv_sg, (double)Ht * inv_sh);
   }
   bool valid = best.f >= 0 && best.chg > kRtEps;   // CPUExpandEntry::IsValid
@@ -1008,7 +1053,7 @@ void launch_hist(const Wave& w, int level, cudaStream_t s) {
 }
 void launch_scan(const Wave& w, int level, cudaStream_t s) {
   int pairs = level == 0 ? 1 : (1 << (level - 1));
-  k_scan<<<dim3(pairs, w.n_jobs), 2 * w.groups * scan_chunks(w.groups) * 32, 0, s>>>(w, level);
+  k_scan<<<dim3(pairs, w.n_jobs), w.groups * scan_chunks(w.groups) * 32, 0, s>>>(w, level);
 }
 void launch_plan_part(const Wave& w, int level, cudaStream_t s) { k_plan_part<<<w.n_jobs, 256, 0, s>>>(w, level); }
 void launch_part_count(const Wave& w, int level, cudaStream_t s) {
