@@ -253,8 +253,13 @@ def main():
     ips = args.inds_per_step
 
     def step_genes(s):
-        base = (s * world + rank) * ips
-        return [genes[(base + i) % pop] for i in range(ips)]
+        """This rank's share of step s: the step's world x ips consecutive individuals are dealt to the ranks
+        deepest-first round-robin, exactly as gentun_b200.sharding does for a population."""
+        from gentun_b200.sharding import shard_plan
+        base = s * world * ips
+        batch = [genes[(base + i) % pop] for i in range(world * ips)]
+        mine = shard_plan([g["max_depth"] for g in batch], world)[rank]
+        return [batch[i] for i in mine]
 
     # ---- resident arm: binned folds in HBM before the timed region
     eng = Engine(x, y, device=local_rank, collect_timing=True)

@@ -889,7 +889,10 @@ __global__ void __launch_bounds__(256) k_part_scatter(Wave w, int level) {
 // raw value < threshold); the prediction is updated in place, test rows add their
 // metric term, train rows record the gradient range of the next round.
 __global__ void __launch_bounds__(256) k_predict(Wave w) {
-  const int j = blockIdx.y;
+  // grid.x = job, grid.y = row chunk: CTAs that are scheduled together work on the same rows of different jobs,
+  // and the jobs of one fold share the fold's bin matrix and labels, so those lines are served from L2
+  const int j = blockIdx.x;
+  const int chunk = blockIdx.y;
   const JobState& js = w.js[j];
   if (!js.active) return;
   const JobParams jp = w.jp[j];
@@ -900,7 +903,7 @@ __global__ void __launch_bounds__(256) k_predict(Wave w) {
   for (int i = threadIdx.x; i < n_nodes; i += blockDim.x) s_tree[i] = tree[i];
   __syncthreads();
   float* pred = w.pred + (size_t)j * w.n;
-  const long long r0 = (long long)blockIdx.x * kPredRows;
+  const long long r0 = (long long)chunk * kPredRows;
   float gm = 0.f, hm = 0.f;
   double msum = 0.0;
   for (int i = threadIdx.x; i < kPredRows; i += blockDim.x) {
@@ -951,7 +954,7 @@ __global__ void __launch_bounds__(256) k_predict(Wave w) {
   if (threadIdx.x == 0) {
     double t = 0;
     for (int q = 0; q < 8; ++q) t += s_m[q];
-    w.mpart[(size_t)j * w.pred_chunks + blockIdx.x] = t;
+    w.mpart[(size_t)j * w.pred_chunks + chunk] = t;
   }
 }
 
@@ -1062,7 +1065,7 @@ void launch_part_count(const Wave& w, int level, cudaStream_t s) {
 void launch_part_scatter(const Wave& w, int level, cudaStream_t s) {
   k_part_scatter<<<dim3(part_items_bound(w, level), w.n_jobs), 256, 0, s>>>(w, level);
 }
-void launch_predict(const Wave& w, cudaStream_t s) { k_predict<<<dim3(w.pred_chunks, w.n_jobs), 256, 0, s>>>(w); }
+void launch_predict(const Wave& w, cudaStream_t s) { k_predict<<<dim3(w.n_jobs, w.pred_chunks), 256, 0, s>>>(w); }
 void launch_round_end(const Wave& w, int first, double* fitness_out, int* rounds_out, cudaStream_t s) {
   k_round_end<<<w.n_inds, 32, 0, s>>>(w, first, fitness_out, rounds_out);
 }

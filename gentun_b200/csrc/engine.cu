@@ -347,6 +347,7 @@ int eval_impl(gt_engine* e, int n_ind, const double* genes, const gt_fit_opts* o
   const int part_cap = (int)(nt_stride / gt::kPartRows + 514);
   const int pair_cap = 512;
   const int pred_chunks = (int)((n + gt::kPredRows - 1) / gt::kPredRows);
+  if (pred_chunks > 65535) return fail(GT_ERR_ARG, "n=%lld rows exceeds this build's limit of %lld", (long long)n, 65535ll * gt::kPredRows);
 
   // order by depth so that a wave's level loop is not held open by one deep individual
   std::vector<int> order(n_ind);

@@ -54,3 +54,20 @@ def evaluate_sharded(engine, genes_list, params, local_eval=None):
     if np.isnan(out).any():
         raise RuntimeError("gentun_b200: fitness all-gather left %d individuals unevaluated" % int(np.isnan(out).sum()))
     return out
+
+
+def init_distributed(backend="nccl"):
+    """Convenience for scripts launched with torchrun (one process per GPU): binds this rank to its GPU and
+    joins the process group.  After this, Population.get_fittest() shards each generation's pending individuals
+    over the ranks; run the same seeded script on every rank."""
+    import os
+    import torch
+    import torch.distributed as dist
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if backend == "nccl":
+        torch.cuda.set_device(local_rank)
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    if not dist.is_initialized():
+        kwargs = {"device_id": torch.device("cuda", local_rank)} if backend == "nccl" else {}
+        dist.init_process_group(backend, **kwargs)
+    return dist.get_rank(), dist.get_world_size()
