@@ -14,8 +14,6 @@
 // |q| <= 2^19) so that all histogram arithmetic is integer: shared-memory partials are int32
 // (native ATOMS.ADD), global cells are int64, parent - child subtraction is exact and the result
 // does not depend on summation order.
-#include <cstdlib>
-
 #include "common.cuh"
 #include "kernels.h"
 
@@ -23,7 +21,6 @@ namespace gt {
 namespace {
 
 constexpr float kRtEps = 1e-6f;
-constexpr int kHistThreads = 256;
 constexpr int kHistSmem = 2 * kBins * kLanes * (int)sizeof(int);   // g plane + h plane = 64 KiB
 
 // ------------------------------------------------------------------ split arithmetic
@@ -606,7 +603,7 @@ __global__ void __launch_bounds__(512, 2) k_scan(Wave w, int level) {
   __shared__ Cand s_c[16][2];
   {
     longlong2 ab = make_longlong2(0, 0), as = make_longlong2(0, 0);
-#pragma unroll 4
+#pragma unroll 8
     for (int b = b_lo; b < b_hi; ++b) {
       const longlong2 eb = load_cell(hbuilt, nar_b, goff + (size_t)b * kLanes);
       ab.x += eb.x; ab.y += eb.y;
@@ -631,12 +628,22 @@ __global__ void __launch_bounds__(512, 2) k_scan(Wave w, int level) {
   const long long hmin_q = (long long)ceil((double)jp.mcw * (double)js.sh);
   cb.e1 = cb.e2 = cs.e1 = cs.e2 = -3.0e38f; cb.b1 = cs.b1 = -1; cb.GL1 = cb.HL1 = cs.GL1 = cs.HL1 = 0; cb.smax = cs.smax = 0.f;
   const int hi = factive ? min(b_hi, nc) : b_lo;
-  for (int b = b_lo; b < hi; ++b) {
-    const longlong2 eb = load_cell(hbuilt, nar_b, goff + (size_t)b * kLanes);
-    child_step(cb, jp, eb, b, true, hmin_q, isg, ish);
-    if (has_sib) {
-      const longlong2 pe = load_cell(hpar, nar_p, goff + (size_t)b * kLanes);
-      child_step(cs, jp, make_longlong2(pe.x - eb.x, pe.y - eb.y), b, true, hmin_q, isg, ish);
+  {
+    // the loop body is long and in-order, so the next bin's cells are requested before this bin is evaluated
+    longlong2 eb = make_longlong2(0, 0), pe = make_longlong2(0, 0);
+    if (b_lo < hi) {
+      eb = load_cell(hbuilt, nar_b, goff + (size_t)b_lo * kLanes);
+      if (has_sib) pe = load_cell(hpar, nar_p, goff + (size_t)b_lo * kLanes);
+    }
+    for (int b = b_lo; b < hi; ++b) {
+      longlong2 eb_n = make_longlong2(0, 0), pe_n = make_longlong2(0, 0);
+      if (b + 1 < hi) {
+        eb_n = load_cell(hbuilt, nar_b, goff + (size_t)(b + 1) * kLanes);
+        if (has_sib) pe_n = load_cell(hpar, nar_p, goff + (size_t)(b + 1) * kLanes);
+      }
+      child_step(cb, jp, eb, b, true, hmin_q, isg, ish);
+      if (has_sib) child_step(cs, jp, make_longlong2(pe.x - eb.x, pe.y - eb.y), b, true, hmin_q, isg, ish);
+      eb = eb_n; pe = pe_n;
     }
   }
   float v0 = cb.e1, v1 = cb.smax, v2 = cs.e1, v3 = cs.smax;
@@ -696,48 +703,58 @@ __global__ void __launch_bounds__(512, 2) k_scan(Wave w, int level) {
   }
   if (lane == 0) { s_c[warp][0] = bestc[0]; s_c[warp][1] = bestc[1]; }
   __syncthreads();
-  // one thread per child finishes the node: thread 0 the built child, thread 32 the sibling
+  // warp 0 finishes the built child, warp 1 the sibling: lanes merge the warps' candidates with shuffles,
+  // then lanes 0 and 1 each set up one grandchild
   const int side = warp;
-  if (lane != 0 || side > 1 || (side == 1 && !has_sib)) return;
-  Cand best = s_c[0][side];
-  for (int k = 1; k < G * NCH; ++k) {
-    const Cand o = s_c[k][side];
-    if (better(o.chg, o.f, o.b, best.chg, best.f, best.b)) best = o;
+  if (side > 1 || (side == 1 && !has_sib)) return;
+  Cand best = lane < G * NCH ? s_c[lane][side] : Cand{0.0f, -1, -1, 0, 0};
+  for (int d = 8; d; d >>= 1) {
+    const float ochg = __shfl_xor_sync(0xffffffffu, best.chg, d);
+    const int of = __shfl_xor_sync(0xffffffffu, best.f, d);
+    const int ob = __shfl_xor_sync(0xffffffffu, best.b, d);
+    const long long oGL = __shfl_xor_sync(0xffffffffu, best.GL, d);
+    const long long oHL = __shfl_xor_sync(0xffffffffu, best.HL, d);
+    if (better(ochg, of, ob, best.chg, best.f, best.b)) { best.chg = ochg; best.f = of; best.b = ob; best.GL = oGL; best.HL = oHL; }
   }
+  best.chg = __shfl_sync(0xffffffffu, best.chg, 0); best.f = __shfl_sync(0xffffffffu, best.f, 0);
+  best.b = __shfl_sync(0xffffffffu, best.b, 0);
+  best.GL = __shfl_sync(0xffffffffu, best.GL, 0); best.HL = __shfl_sync(0xffffffffu, best.HL, 0);
+  if (lane > 1) return;
   const ChildScan& c = side == 0 ? cb : cs;
   const int node = side == 0 ? bnode : snode;
   const long long Gt = c.Gt, Ht = c.Ht;
   Node& nd = nodes[node];
-  if (level == 0) {
-    nd.root_gain = c.root_gain;
-    nd.leaf = jp.eta * calc_weight(jp, (double)Gt * inv_sg, (double)Ht * inv_sh);
-  }
   bool valid = best.f >= 0 && best.chg > kRtEps;   // CPUExpandEntry::IsValid
   if (valid) {
     const double hl = (double)best.HL * inv_sh, hr = (double)(Ht - best.HL) * inv_sh;
     if (hl == 0.0 || hr == 0.0) valid = false;
     if (best.chg < jp.gamma) valid = false;
   }
-  nd.loss_chg = best.chg;
-  if (!valid) {
-    nd.state = kLeaf;
-    tree[node] = TreeNode{nd.leaf, (int16_t)-1, (uint8_t)0, (uint8_t)kLeaf};
-    return;
+  float own_leaf = nd.leaf;
+  if (level == 0) own_leaf = jp.eta * calc_weight(jp, (double)Gt * inv_sg, (double)Ht * inv_sh);
+  if (lane == 0) {
+    if (level == 0) { nd.root_gain = c.root_gain; nd.leaf = own_leaf; }
+    nd.loss_chg = best.chg;
+    if (!valid) {
+      nd.state = kLeaf;
+      tree[node] = TreeNode{own_leaf, (int16_t)-1, (uint8_t)0, (uint8_t)kLeaf};
+    } else {
+      nd.state = kSplit; nd.feat = (int16_t)best.f; nd.bin = (uint8_t)best.b;
+      tree[node] = TreeNode{0.f, (int16_t)best.f, (uint8_t)best.b, (uint8_t)kSplit};
+    }
   }
-  nd.state = kSplit; nd.feat = (int16_t)best.f; nd.bin = (uint8_t)best.b;
-  tree[node] = TreeNode{0.f, (int16_t)best.f, (uint8_t)best.b, (uint8_t)kSplit};
+  if (!valid) return;
   const uint8_t child_state = (level + 1 < jp.max_depth) ? kOpen : kLeaf;   // Driver::IsChildValid
-  const long long cg[2] = {best.GL, Gt - best.GL}, chh[2] = {best.HL, Ht - best.HL};
-  for (int sd = 0; sd < 2; ++sd) {
-    Node& chn = nodes[2 * node + 1 + sd];
-    const double g = (double)cg[sd] * inv_sg, h = (double)chh[sd] * inv_sh;
-    chn.G = cg[sd]; chn.H = chh[sd];
-    chn.leaf = jp.eta * calc_weight(jp, g, h);
-    chn.root_gain = calc_gain(jp, g, h);
-    chn.loss_chg = 0.f; chn.feat = -1; chn.bin = 0; chn.state = child_state;
-    chn.begin = 0; chn.cnt = 0; chn.buf = 0;
-    tree[2 * node + 1 + sd] = TreeNode{chn.leaf, (int16_t)-1, (uint8_t)0, child_state};
-  }
+  const int sd = lane;   // lane 0: left grandchild, lane 1: right grandchild
+  const long long cgq = sd == 0 ? best.GL : Gt - best.GL, chq = sd == 0 ? best.HL : Ht - best.HL;
+  Node& chn = nodes[2 * node + 1 + sd];
+  const double g = (double)cgq * inv_sg, h = (double)chq * inv_sh;
+  chn.G = cgq; chn.H = chq;
+  chn.leaf = jp.eta * calc_weight(jp, g, h);
+  chn.root_gain = calc_gain(jp, g, h);
+  chn.loss_chg = 0.f; chn.feat = -1; chn.bin = 0; chn.state = child_state;
+  chn.begin = 0; chn.cnt = 0; chn.buf = 0;
+  tree[2 * node + 1 + sd] = TreeNode{chn.leaf, (int16_t)-1, (uint8_t)0, child_state};
 }
 
 // ------------------------------------------------------------------ X7: stable row partition
@@ -1050,8 +1067,7 @@ void launch_plan_hist(const Wave& w, int level, cudaStream_t s) { k_plan_hist<<<
 void launch_hist_zero(const Wave& w, int level, cudaStream_t s) { k_hist_zero<<<dim3(32, w.n_jobs), 256, 0, s>>>(w, level); }
 void launch_hist(const Wave& w, int level, cudaStream_t s) {
   int cap = hist_items_bound(w, level);
-  static const bool force_single = getenv("GT_HIST_SINGLE_GROUP") != nullptr;   // tuning switch
-  if (w.groups % 2 == 0 && !force_single) k_hist<4><<<dim3(cap * (w.groups / 2), w.n_jobs), 512, 2 * kHistSmem, s>>>(w, level);
+  if (w.groups % 2 == 0) k_hist<4><<<dim3(cap * (w.groups / 2), w.n_jobs), 512, 2 * kHistSmem, s>>>(w, level);
   else k_hist<2><<<dim3(cap * w.groups, w.n_jobs), 256, kHistSmem, s>>>(w, level);
 }
 void launch_scan(const Wave& w, int level, cudaStream_t s) {
