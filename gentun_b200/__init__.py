@@ -8,8 +8,9 @@ from .population import Population, GridPopulation
 from .genetics import Individual, XgboostIndividual, random_log_uniform
 from .cv_model import GentunModel, XgboostModel
 from .engine import Engine, EngineError, clear_engines
+from .distributed import DistributedPopulation, DistributedGridPopulation, GentunWorker
 
 __all__ = ["GeneticAlgorithm", "RussianRouletteGA", "Population", "GridPopulation", "Individual",
            "XgboostIndividual", "GentunModel", "XgboostModel", "Engine", "EngineError", "clear_engines",
-           "random_log_uniform"]
+           "random_log_uniform", "DistributedPopulation", "DistributedGridPopulation", "GentunWorker"]
 __version__ = "0.1.0"
