@@ -245,10 +245,10 @@ __global__ void __launch_bounds__(256) k_plan_hist(Wave w, int level) {
   // each thread owns up to two parents (2 * 256 >= 2^(kMaxDepth - 1))
   const int n_par = level == 0 ? 1 : (1 << (level - 1));
   const int first = level == 0 ? 0 : level_first(level - 1);
-  int bnode[2], chunks[2], shr[2];
+  int bnode[2], chunks[2], shr[2], single[2];
   for (int s2 = 0; s2 < 2; ++s2) {
     const int pi = 2 * threadIdx.x + s2;
-    bnode[s2] = -1; chunks[s2] = 0; shr[s2] = 0;
+    bnode[s2] = -1; chunks[s2] = 0; shr[s2] = 0; single[s2] = 0;
     if (pi >= n_par) continue;
     if (level == 0) {
       bnode[s2] = 0;
@@ -256,7 +256,10 @@ __global__ void __launch_bounds__(256) k_plan_hist(Wave w, int level) {
       const int p = first + pi;
       if (nodes[p].state != kSplit) continue;
       const int l = 2 * p + 1, r = 2 * p + 2;
-      bnode[s2] = nodes[l].cnt <= nodes[r].cnt ? l : r;
+      const bool lo = nodes[l].state == kOpen, ro = nodes[r].state == kOpen;
+      if (!lo && !ro) continue;                       // both children were settled as leaves when the parent split
+      single[s2] = !(lo && ro);
+      bnode[s2] = single[s2] ? (lo ? l : r) : (nodes[l].cnt <= nodes[r].cnt ? l : r);
     }
     const uint32_t cnt = nodes[bnode[s2]].cnt;
     chunks[s2] = (int)((cnt + kHistRows - 1) / kHistRows);
@@ -287,7 +290,7 @@ __global__ void __launch_bounds__(256) k_plan_hist(Wave w, int level) {
       items[ni] = HistItem{bnode[s2], bn.begin + b, cnt, shr[s2] | ((int)bn.buf << 1)};
     }
     if (shr[s2]) { if (nz < w.hist_cap) zl[nz] = bnode[s2]; ++nz; }
-    if (np < w.pair_cap) pairs[np] = level == 0 ? PairRec{-1, 0} : PairRec{(bnode[s2] - 1) >> 1, (bnode[s2] & 1) ? 0 : 1};
+    if (np < w.pair_cap) pairs[np] = level == 0 ? PairRec{-1, 0, 1} : PairRec{(bnode[s2] - 1) >> 1, (bnode[s2] & 1) ? 0 : 1, single[s2]};
     ++np;
     rows_mine += bn.cnt;
   }
@@ -572,7 +575,7 @@ __global__ void __launch_bounds__(512, 2) k_scan(Wave w, int level) {
   const int grp = warp / NCH, ch = warp % NCH;
   Node* nodes = w.nodes + (size_t)j * kNodeCap;
   TreeNode* tree = w.tree + (size_t)j * kNodeCap;
-  const bool has_sib = level > 0;
+  const bool has_sib = level > 0 && !pr.single;
   const int bnode = level == 0 ? 0 : 2 * pr.parent + 1 + pr.build_right;       // histogram built by k_hist
   const int snode = level == 0 ? 0 : 2 * pr.parent + 2 - pr.build_right;       // its sibling
   const FoldDev& fd = w.folds[jp.fold];
@@ -744,9 +747,13 @@ __global__ void __launch_bounds__(512, 2) k_scan(Wave w, int level) {
     }
   }
   if (!valid) return;
-  const uint8_t child_state = (level + 1 < jp.max_depth) ? kOpen : kLeaf;   // Driver::IsChildValid
   const int sd = lane;   // lane 0: left grandchild, lane 1: right grandchild
   const long long cgq = sd == 0 ? best.GL : Gt - best.GL, chq = sd == 0 ? best.HL : Ht - best.HL;
+  // Driver::IsChildValid; in addition a child whose hessian sum is below 2 * min_child_weight has no valid
+  // candidate (both sides need H >= min_child_weight), so evaluating it could only make it a leaf: settle that now
+  // and spare its histogram, scan and partition
+  const bool can_split = hmin_q <= 0 || chq >= 2 * hmin_q;
+  const uint8_t child_state = (level + 1 < jp.max_depth && can_split) ? kOpen : kLeaf;
   Node& chn = nodes[2 * node + 1 + sd];
   const double g = (double)cgq * inv_sg, h = (double)chq * inv_sh;
   chn.G = cgq; chn.H = chq;
@@ -774,6 +781,7 @@ __global__ void __launch_bounds__(256) k_plan_part(Wave w, int level) {
     if (li >= n_lvl) continue;
     const Node& nd = nodes[first + li];
     if (nd.state != kSplit) continue;
+    if (nodes[2 * (first + li) + 1].state != kOpen && nodes[2 * (first + li) + 2].state != kOpen) continue;   // no child needs its rows
     nid[s2] = first + li;
     chunks[s2] = (int)((nd.cnt + kPartRows - 1) / kPartRows);
   }

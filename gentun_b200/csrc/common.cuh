@@ -42,7 +42,7 @@ struct TreeNode {      // compact record read by the prediction kernel, 8 B
 };
 
 struct HistItem { int node; uint32_t begin; uint32_t cnt; int flags; };  // flags bit0: shared (atomic flush), bit1: buf
-struct PairRec { int parent; int build_right; };
+struct PairRec { int parent; int build_right; int single; };   // single: only the built child is evaluated (its sibling is already a leaf)
 struct PartItem { int node; uint32_t begin; uint32_t cnt; int first_item; int n_items; uint32_t node_begin; uint32_t node_cnt; int buf; };
 
 struct JobParams {     // constant over one evaluation

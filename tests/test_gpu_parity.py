@@ -208,6 +208,13 @@ def test_tree_structure_and_row_partitions(wine_pair):
                 # reused by its grandchildren; leaves and the deepest evaluated level stay intact
                 if not (tree["feat"][nid] == -1 or depth == D - 1):
                     continue
+                if nr["count"][nid] == 0 and len(rows) > 0:
+                    # both children of its parent were settled as leaves when the parent split (hessian sum
+                    # below 2 * min_child_weight): such a parent is never partitioned
+                    sib = nid + 1 if nid % 2 == 1 else nid - 1
+                    assert nid > 0 and nr["count"][sib] == 0 and tree["feat"][nid] == -1 and tree["feat"][sib] == -1
+                    assert len(rows) < 2 * max(g["min_child_weight"], 1)
+                    continue
                 seg = rs[nr["buf"][nid], nr["begin"][nid]: nr["begin"][nid] + nr["count"][nid]]
                 assert np.array_equal(seg.astype(np.int64), rows), (i, k, nid)
                 checked += 1
