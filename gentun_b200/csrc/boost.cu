@@ -140,6 +140,8 @@ __global__ void __launch_bounds__(256) k_init_wave(Wave w) {
 __global__ void __launch_bounds__(256) k_grad(Wave w) {
   const int j = blockIdx.y;
   const JobState& js = w.js[j];
+  // a new round: the per-level pair lists start empty (done by one thread whether or not job 0 is still training)
+  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) { w.counters[5] = 0ull; w.counters[6] = 0ull; }
   if (!js.active) return;
   const JobParams jp = w.jp[j];
   const FoldDev fd = w.folds[jp.fold];
@@ -150,6 +152,7 @@ __global__ void __launch_bounds__(256) k_grad(Wave w) {
   Node* nodes = w.nodes + (size_t)j * kNodeCap;
   if (blockIdx.x == 0)
     for (int i = 1 + threadIdx.x; i < kNodeCap; i += blockDim.x) nodes[i].state = kAbsent;
+
   const uint64_t skey = stream_key(1u, (uint32_t)jp.fold, (uint32_t)round, 0u);
   const bool sub = jp.subsample < 1.0f;
   long long sG = 0, sH = 0;
@@ -204,6 +207,7 @@ __global__ void __launch_bounds__(256) k_plan_hist(Wave w, int level) {
   __shared__ uint32_t s_mask[kMaskWords];
   __shared__ uint32_t s_in[kMaskWords];
   if (threadIdx.x == 0) { js.n_hist_items = 0; js.n_pairs = 0; js.n_zero = 0; js.n_part_items = 0; }
+  if (j == 0 && threadIdx.x == 0) w.counters[5 + ((level + 1) & 1)] = 0ull;   // the next level's pair list starts empty
   if (!js.active || level >= jp.max_depth) return;
   const int round = w.is[jp.ind].round;
   // feature sets (colsample_bytree at level 0, colsample_bylevel at every level)
@@ -237,11 +241,12 @@ __global__ void __launch_bounds__(256) k_plan_hist(Wave w, int level) {
   // work items: histogram chunks of the nodes to build, (built, sibling) pairs to evaluate
   Node* nodes = w.nodes + (size_t)j * kNodeCap;
   HistItem* items = w.hitems + (size_t)j * w.hist_cap;
-  PairRec* pairs = w.pairs + (size_t)j * w.pair_cap;
   int* zl = w.zlist + (size_t)j * w.hist_cap;
   __shared__ int s_scan[3][256];
   __shared__ unsigned long long s_rows;
+  __shared__ int s_pair_base;
   if (threadIdx.x == 0) s_rows = 0ull;
+
   // each thread owns up to two parents (2 * 256 >= 2^(kMaxDepth - 1))
   const int n_par = level == 0 ? 1 : (1 << (level - 1));
   const int first = level == 0 ? 0 : level_first(level - 1);
@@ -278,6 +283,9 @@ __global__ void __launch_bounds__(256) k_plan_hist(Wave w, int level) {
     for (int q = 0; q < 3; ++q) s_scan[q][threadIdx.x] += t[q];
     __syncthreads();
   }
+  if (threadIdx.x == 255) s_pair_base = (int)atomicAdd(&w.counters[5 + (level & 1)], (unsigned long long)s_scan[1][255]);
+  __syncthreads();
+  PairRec* pairs = w.pairs + s_pair_base;
   int ni = s_scan[0][threadIdx.x] - v[0], np = s_scan[1][threadIdx.x] - v[1], nz = s_scan[2][threadIdx.x] - v[2];
   unsigned long long rows_mine = 0;
   for (int s2 = 0; s2 < 2; ++s2) {
@@ -290,7 +298,7 @@ __global__ void __launch_bounds__(256) k_plan_hist(Wave w, int level) {
       items[ni] = HistItem{bnode[s2], bn.begin + b, cnt, shr[s2] | ((int)bn.buf << 1)};
     }
     if (shr[s2]) { if (nz < w.hist_cap) zl[nz] = bnode[s2]; ++nz; }
-    if (np < w.pair_cap) pairs[np] = level == 0 ? PairRec{-1, 0, 1} : PairRec{(bnode[s2] - 1) >> 1, (bnode[s2] & 1) ? 0 : 1, single[s2]};
+    pairs[np] = level == 0 ? PairRec{-1, 0, 1, j} : PairRec{(bnode[s2] - 1) >> 1, (bnode[s2] & 1) ? 0 : 1, single[s2], j};
     ++np;
     rows_mine += bn.cnt;
   }
@@ -298,7 +306,7 @@ __global__ void __launch_bounds__(256) k_plan_hist(Wave w, int level) {
   __syncthreads();
   if (threadIdx.x == 255) {
     js.n_hist_items = min(s_scan[0][255], w.hist_cap);
-    js.n_pairs = min(s_scan[1][255], w.pair_cap);
+    js.n_pairs = s_scan[1][255];
     js.n_zero = min(s_scan[2][255], w.hist_cap);
     if (s_rows) atomicAdd(&w.counters[0], s_rows);
     if (s_scan[1][255]) atomicAdd(&w.counters[1], (unsigned long long)s_scan[1][255]);
@@ -564,12 +572,10 @@ __device__ __forceinline__ void exact_candidate(Cand& best, const JobParams& jp,
 // Pass 1: chunk sums.  Pass 2: with the chunk prefix from shared memory each lane runs EnumerateSplit<+1>
 // over its bins with a branch-free fp32 gain estimate; only candidates within the estimate's error
 // margin of the best one are re-evaluated in the reference's double/float expression order.
-__global__ void __launch_bounds__(512, 2) k_scan(Wave w, int level) {
-  const int j = blockIdx.y;
+__device__ __forceinline__ void scan_pair(const Wave& w, int level, const PairRec pr) {
+  const int j = pr.job;
   const JobState& js = w.js[j];
-  if ((int)blockIdx.x >= js.n_pairs) return;
   const JobParams& jp = w.jp[j];
-  const PairRec pr = w.pairs[(size_t)j * w.pair_cap + blockIdx.x];
   const int G = w.groups, NCH = scan_chunks(G), CB = kBins / NCH;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int grp = warp / NCH, ch = warp % NCH;
@@ -762,6 +768,14 @@ __global__ void __launch_bounds__(512, 2) k_scan(Wave w, int level) {
   chn.loss_chg = 0.f; chn.feat = -1; chn.bin = 0; chn.state = child_state;
   chn.begin = 0; chn.cnt = 0; chn.buf = 0;
   tree[2 * node + 1 + sd] = TreeNode{chn.leaf, (int16_t)-1, (uint8_t)0, child_state};
+}
+
+__global__ void __launch_bounds__(512, 2) k_scan(Wave w, int level) {
+  const int n_pairs = (int)w.counters[5 + (level & 1)];
+  for (int pair_idx = blockIdx.x; pair_idx < n_pairs; pair_idx += gridDim.x) {
+    scan_pair(w, level, w.pairs[pair_idx]);
+    __syncthreads();   // shared scratch is reused by the next pair
+  }
 }
 
 // ------------------------------------------------------------------ X7: stable row partition
@@ -1071,23 +1085,25 @@ void launch_grad(const Wave& w, cudaStream_t s) {
   int chunks = (int)((w.nt_stride + kPredRows - 1) / kPredRows);
   k_grad<<<dim3(chunks, w.n_jobs), 256, 0, s>>>(w);
 }
-void launch_plan_hist(const Wave& w, int level, cudaStream_t s) { k_plan_hist<<<w.n_jobs, 256, 0, s>>>(w, level); }
-void launch_hist_zero(const Wave& w, int level, cudaStream_t s) { k_hist_zero<<<dim3(32, w.n_jobs), 256, 0, s>>>(w, level); }
+// Per-level launches cover only the jobs whose trees reach that level (a prefix of the depth-ordered job array).
+void launch_plan_hist(const Wave& w, int level, cudaStream_t s) { k_plan_hist<<<w.lvl_jobs[level], 256, 0, s>>>(w, level); }
+void launch_hist_zero(const Wave& w, int level, cudaStream_t s) { k_hist_zero<<<dim3(32, w.lvl_jobs[level]), 256, 0, s>>>(w, level); }
 void launch_hist(const Wave& w, int level, cudaStream_t s) {
   int cap = hist_items_bound(w, level);
-  if (w.groups % 2 == 0) k_hist<4><<<dim3(cap * (w.groups / 2), w.n_jobs), 512, 2 * kHistSmem, s>>>(w, level);
-  else k_hist<2><<<dim3(cap * w.groups, w.n_jobs), 256, kHistSmem, s>>>(w, level);
+  if (w.groups % 2 == 0) k_hist<4><<<dim3(cap * (w.groups / 2), w.lvl_jobs[level]), 512, 2 * kHistSmem, s>>>(w, level);
+  else k_hist<2><<<dim3(cap * w.groups, w.lvl_jobs[level]), 256, kHistSmem, s>>>(w, level);
 }
 void launch_scan(const Wave& w, int level, cudaStream_t s) {
-  int pairs = level == 0 ? 1 : (1 << (level - 1));
-  k_scan<<<dim3(pairs, w.n_jobs), w.groups * scan_chunks(w.groups) * 32, 0, s>>>(w, level);
+  const long long bound = (long long)w.lvl_jobs[level] * (level == 0 ? 1 : (1 << (level - 1)));
+  const int grid = (int)(bound < 148 * 4 ? bound : 148 * 4);   // CTAs loop over the wave-wide pair list
+  k_scan<<<grid, w.groups * scan_chunks(w.groups) * 32, 0, s>>>(w, level);
 }
-void launch_plan_part(const Wave& w, int level, cudaStream_t s) { k_plan_part<<<w.n_jobs, 256, 0, s>>>(w, level); }
+void launch_plan_part(const Wave& w, int level, cudaStream_t s) { k_plan_part<<<w.lvl_jobs[level + 1], 256, 0, s>>>(w, level); }
 void launch_part_count(const Wave& w, int level, cudaStream_t s) {
-  k_part_count<<<dim3(part_items_bound(w, level), w.n_jobs), 256, 0, s>>>(w, level);
+  k_part_count<<<dim3(part_items_bound(w, level), w.lvl_jobs[level + 1]), 256, 0, s>>>(w, level);
 }
 void launch_part_scatter(const Wave& w, int level, cudaStream_t s) {
-  k_part_scatter<<<dim3(part_items_bound(w, level), w.n_jobs), 256, 0, s>>>(w, level);
+  k_part_scatter<<<dim3(part_items_bound(w, level), w.lvl_jobs[level + 1]), 256, 0, s>>>(w, level);
 }
 void launch_predict(const Wave& w, cudaStream_t s) { k_predict<<<dim3(w.n_jobs, w.pred_chunks), 256, 0, s>>>(w); }
 void launch_round_end(const Wave& w, int first, double* fitness_out, int* rounds_out, cudaStream_t s) {

@@ -42,7 +42,7 @@ struct TreeNode {      // compact record read by the prediction kernel, 8 B
 };
 
 struct HistItem { int node; uint32_t begin; uint32_t cnt; int flags; };  // flags bit0: shared (atomic flush), bit1: buf
-struct PairRec { int parent; int build_right; int single; };   // single: only the built child is evaluated (its sibling is already a leaf)
+struct PairRec { int parent; int build_right; int single; int job; };   // single: only the built child is evaluated (its sibling is already a leaf)
 struct PartItem { int node; uint32_t begin; uint32_t cnt; int first_item; int n_items; uint32_t node_begin; uint32_t node_cnt; int buf; };
 
 struct JobParams {     // constant over one evaluation
@@ -94,6 +94,7 @@ struct Wave {            // passed by value to kernels
   int objective, metric, num_boost_round, early_stopping_rounds;
   int hist_cap, pair_cap, part_cap;  // per-job record capacities
   int pred_chunks;
+  int lvl_jobs[kMaxDepth + 2];   // jobs whose max_depth exceeds the level; jobs are ordered deepest first, so they form a prefix
   const FoldDev* folds;
   const int* grp_maxnc;  // [nfold][groups] max ncuts inside the group
   JobParams* jp;
@@ -107,12 +108,12 @@ struct Wave {            // passed by value to kernels
   HistEntry* hist;       // arena
   HistItem* hitems;      // [n_jobs][hist_cap]
   int* zlist;            // [n_jobs][hist_cap] nodes whose histogram must be cleared
-  PairRec* pairs;        // [n_jobs][pair_cap]
+  PairRec* pairs;        // [n_jobs * pair_cap] pairs of the current level, all jobs, appended by the planners
   PartItem* pitems;      // [n_jobs][part_cap]
   int* pleft;            // [n_jobs][part_cap]
   double* mpart;         // [n_jobs][pred_chunks] per-CTA metric partial sums
   double* trace;         // [n_inds][num_boost_round] or null
-  unsigned long long* counters;  // [0] rows through hist, [1] node histograms built, [2] active individuals
+  unsigned long long* counters;  // [0] rows through hist, [1] node histograms built, [2] active individuals, [5 + level parity] pairs of the level
 };
 
 // counter-based generator (definition shared with the oracle by specification)

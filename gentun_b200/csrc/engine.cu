@@ -442,6 +442,7 @@ int eval_impl(gt_engine* e, int n_ind, const double* genes, const gt_fit_opts* o
     std::vector<gt::IndState> h_is(inds);
     size_t hoff = 0;
     int Dmax = 1;
+    int lvl_jobs[gt::kMaxDepth + 2] = {0};   // jobs that still grow their tree at each level (jobs are ordered deepest first)
     for (int q = 0; q < inds; ++q) {
       const int src = order[wv.first + q];
       const double* g = genes + (size_t)src * GT_NUM_GENES;
@@ -450,6 +451,7 @@ int eval_impl(gt_engine* e, int n_ind, const double* genes, const gt_fit_opts* o
       is.active = 1; is.out_index = src;
       const int D = (int)g[2];
       Dmax = std::max(Dmax, D);
+      for (int d = 0; d < D; ++d) lvl_jobs[d] += nfold;
       for (int k = 0; k < nfold; ++k) {
         gt::JobParams& p = h_jp[q * nfold + k];
         memset(&p, 0, sizeof(p));
@@ -483,6 +485,7 @@ int eval_impl(gt_engine* e, int n_ind, const double* genes, const gt_fit_opts* o
     w.objective = o->objective; w.metric = o->metric; w.num_boost_round = o->num_boost_round;
     w.early_stopping_rounds = o->early_stopping_rounds;
     w.hist_cap = hist_cap; w.pair_cap = pair_cap; w.part_cap = part_cap; w.pred_chunks = pred_chunks;
+    for (int d = 0; d < gt::kMaxDepth + 2; ++d) w.lvl_jobs[d] = lvl_jobs[d];
     w.folds = fs->d_folds.p; w.grp_maxnc = fs->d_grp_maxnc.p;
     w.jp = d_jp.p; w.js = d_js.p; w.is = d_is.p; w.nodes = d_nodes.p; w.tree = d_tree.p; w.pred = d_pred.p;
     w.gq = d_gq.p; w.ridx = d_ridx.p; w.hist = d_hist.p; w.hitems = d_hitems.p; w.zlist = d_zlist.p;
