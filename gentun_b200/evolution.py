@@ -1,10 +1,24 @@
-"""Genetic-algorithm drivers (mirror of gentun/algorithms.py:9-99).  Selection, crossover and
-mutation stay in host Python; only get_fittest() reaches the GPU."""
+"""Genetic-algorithm drivers.
+
+Behavioural mirror of gentun/algorithms.py:9-99: the same console lines, the same use of Python's module-level
+`random` in the same order (Appendix B of SURVEY.md), so a seeded run breeds the same offspring.  Only
+`population.get_fittest()` reaches the GPU; selection, crossover and mutation are host Python.
+"""
 import random
+
+_BANNER = "Starting genetic algorithm...\n"
+
+
+def _announce(generation, fittest):
+    """The three progress lines of the reference (fitness rounded to 4 decimals)."""
+    print("Evaluating generation #{}...".format(generation))
+    print("Fittest individual is:")
+    print(fittest)
+    print("Fitness value is: {}\n".format(round(fittest.get_fitness(), 4)))
 
 
 class GeneticAlgorithm(object):
-    """Tournament selection with optional elitism."""
+    """Generational GA: optional elitism, tournament selection, uniform crossover, per-gene mutation."""
 
     def __init__(self, population, tournament_size=5, elitism=True):
         self.population = population
@@ -16,43 +30,52 @@ class GeneticAlgorithm(object):
     def get_population_type(self):
         return self.population.__class__
 
-    def _empty_like(self, members):
-        return self.get_population_type()(self.population.get_species(), self.x_train, self.y_train,
-                                          individual_list=members, maximize=self.population.get_fitness_criteria())
+    def _spawn_population(self, members):
+        """A population of the same class around `members`.  The reference re-creates the population class with
+        exactly these arguments for every generation and every tournament, which is why engines and broker
+        credentials are kept outside the instance."""
+        source = self.population
+        return self.get_population_type()(source.get_species(), self.x_train, self.y_train, individual_list=members,
+                                          maximize=source.get_fitness_criteria())
 
     def run(self, max_generations):
-        print("Starting genetic algorithm...\n")
+        print(_BANNER)
         while self.generation <= max_generations:
             self.evolve_population()
             self.generation += 1
 
-    def _report(self):
-        print("Evaluating generation #{}...".format(self.generation))
-        fittest = self.population.get_fittest()
-        print("Fittest individual is:")
-        print(fittest)
-        print("Fitness value is: {}\n".format(round(fittest.get_fitness(), 4)))
-        return fittest
+    def tournament_select(self):
+        size = self.population.get_size()
+        contenders = [self.population[i] for i in random.sample(range(size), self.tournament_size)]
+        return self._spawn_population(contenders).get_fittest()
 
     def evolve_population(self):
-        self._report()
-        offspring = self._empty_like([])
+        _announce(self.generation, self.population.get_fittest())
+        next_generation = self._spawn_population([])
         if self.elitism:
-            offspring.add_individual(self.population.get_fittest())
-        target = self.population.get_size()
-        while offspring.get_size() < target:
-            child = self.tournament_select().reproduce(self.tournament_select())
+            next_generation.add_individual(self.population.get_fittest())   # the same object: its fitness is kept
+        wanted = self.population.get_size()
+        while next_generation.get_size() < wanted:
+            mother = self.tournament_select()
+            father = self.tournament_select()
+            child = mother.reproduce(father)
             child.mutate()
-            offspring.add_individual(child)
-        self.population = offspring
+            next_generation.add_individual(child)
+        self.population = next_generation
 
-    def tournament_select(self):
-        drawn = random.sample(range(self.population.get_size()), self.tournament_size)
-        return self._empty_like([self.population[i] for i in drawn]).get_fittest()
+
+def _roulette_weights(scores, maximize, eps):
+    """Selection weights of the Genetic-CNN paper: fitness (or its inverse) shifted so the worst gets zero."""
+    raw = list(scores) if maximize else [1 / (score + eps) for score in scores]
+    floor = min(raw)
+    shifted = [value - floor for value in raw]
+    if sum(shifted) == .0:
+        shifted = [1. for _ in shifted]
+    return shifted
 
 
 class RussianRouletteGA(GeneticAlgorithm):
-    """Fitness-proportional selection of the Genetic CNN paper."""
+    """Fitness-proportional resampling, then pairwise crossover or mutation."""
 
     def __init__(self, population, crossover_probability=0.2, mutation_probability=0.8):
         super(RussianRouletteGA, self).__init__(population)
@@ -60,22 +83,19 @@ class RussianRouletteGA(GeneticAlgorithm):
         self.mutation_probability = mutation_probability
 
     def evolve_population(self, eps=1e-15):
-        self._report()
-        size = self.population.get_size()
-        scores = [self.population[i].get_fitness() for i in range(size)]
-        weights = scores if self.population.get_fitness_criteria() else [1 / (s + eps) for s in scores]
-        floor = min(weights)
-        weights = [wgt - floor for wgt in weights]
-        if sum(weights) == .0:
-            weights = [1. for _ in range(size)]
-        chosen = random.choices(range(size), weights=weights, k=size)
-        offspring = self._empty_like([self.population[i].copy() for i in chosen])
-        for i in range(offspring.get_size() // 2):
+        _announce(self.generation, self.population.get_fittest())
+        current = self.population
+        size = current.get_size()
+        weights = _roulette_weights([current[i].get_fitness() for i in range(size)], current.get_fitness_criteria(), eps)
+        picks = random.choices(range(size), weights=weights, k=size)
+        resampled = self._spawn_population([current[i].copy() for i in picks])
+        for i in range(resampled.get_size() // 2):
+            first, second = resampled[i], resampled[i + 1]
             if random.random() < self.crossover_probability:
-                offspring[i].crossover(offspring[i + 1])
-            else:
-                if random.random() < self.mutation_probability:
-                    offspring[i].mutate()
-                if random.random() < self.mutation_probability:
-                    offspring[i + 1].mutate()
-        self.population = offspring
+                first.crossover(second)
+                continue
+            if random.random() < self.mutation_probability:
+                first.mutate()
+            if random.random() < self.mutation_probability:
+                second.mutate()
+        self.population = resampled
