@@ -650,8 +650,13 @@ __device__ __forceinline__ void scan_pair(const Wave& w, int level, const PairRe
         eb_n = load_cell(hbuilt, nar_b, goff + (size_t)(b + 1) * kLanes);
         if (has_sib) pe_n = load_cell(hpar, nar_p, goff + (size_t)(b + 1) * kLanes);
       }
-      child_step(cb, jp, eb, b, true, hmin_q, isg, ish);
-      if (has_sib) child_step(cs, jp, make_longlong2(pe.x - eb.x, pe.y - eb.y), b, true, hmin_q, isg, ish);
+      // a bin that is empty for every feature of the warp (common in small nodes) changes no prefix and offers no
+      // candidate: skip both evaluations.  (If the parent's cell is zero, so are both children's.)
+      const bool occupied = has_sib ? ((pe.x | pe.y | eb.x | eb.y) != 0) : ((eb.x | eb.y) != 0);
+      if (__any_sync(__activemask(), occupied)) {
+        child_step(cb, jp, eb, b, true, hmin_q, isg, ish);
+        if (has_sib) child_step(cs, jp, make_longlong2(pe.x - eb.x, pe.y - eb.y), b, true, hmin_q, isg, ish);
+      }
       eb = eb_n; pe = pe_n;
     }
   }
