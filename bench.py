@@ -55,7 +55,10 @@ def describe(wl, args, world):
                     "%d boosting rounds" % (n, f, pop, nfold, rounds) if wl == "c3" else wl,
         "rows": n, "features": f, "nfold": nfold, "num_boost_round": rounds, "population": pop,
         "individuals_per_step_per_gpu": args.inds_per_step,
-        "step": "one gt_engine_eval over consecutive individuals of the population seeded with random.seed(20240601)",
+        "step": "the population seeded with random.seed(20240601) is dealt once into %d cost-balanced shards of %d "
+                "individuals (gentun_b200.sharding.shard_plan); in step s rank r runs ONE gt_engine_eval on shard "
+                "(s*n_gpus + r) mod %d, so per-GPU work is the same at every n_gpus and 8 GPUs evaluate one whole "
+                "generation per step" % (pop // args.inds_per_step, args.inds_per_step, pop // args.inds_per_step),
         "l2": "inputs exceed L2: binned folds %d MB + per-job state > 126 MB" % (nfold * n * ((f + 31) // 32 * 32) >> 20),
         "parallelism": "population sharded over %d GPU(s), fitness all-gather" % world,
     }
@@ -239,6 +242,7 @@ def main():
     torch.cuda.set_device(local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # stdout carries the JSON line and nothing else
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     def barrier():
@@ -252,14 +256,15 @@ def main():
     params = dict(nfold=nfold, num_boost_round=rounds, early_stopping_rounds=100)
     ips = args.inds_per_step
 
+    from gentun_b200.sharding import fit_cost, shard_plan
+    if pop % ips:
+        raise SystemExit("--inds-per-step must divide the population size %d" % pop)
+    shards = shard_plan([fit_cost(g) for g in genes], pop // ips)
+
     def step_genes(s):
-        """This rank's share of step s: the step's world x ips consecutive individuals are dealt to the ranks
-        deepest-first round-robin, exactly as gentun_b200.sharding does for a population."""
-        from gentun_b200.sharding import shard_plan
-        base = s * world * ips
-        batch = [genes[(base + i) % pop] for i in range(world * ips)]
-        mine = shard_plan([g["max_depth"] for g in batch], world)[rank]
-        return [batch[i] for i in mine]
+        """This rank's share of step s: one of the population's cost-balanced shards (the same dealing
+        gentun_b200.sharding does for a generation on pop // ips GPUs), so every rank always has one shard's work."""
+        return [genes[i] for i in shards[(s * world + rank) % len(shards)]]
 
     # ---- resident arm: binned folds in HBM before the timed region
     eng = Engine(x, y, device=local_rank, collect_timing=True)
@@ -293,6 +298,10 @@ def main():
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     dev_ms_max, wall_ms_max = float(t[0]), float(t[1])
+    rank_ms = torch.zeros(world, dtype=torch.float64, device="cuda")
+    rank_ms[rank] = dev_ms / args.steps
+    if world > 1:
+        dist.all_reduce(rank_ms)
     value = world * ips * args.steps / (wall_ms_max / 1e3)
 
     # ---- end-to-end arm: host buffers in, fitness out, through the C ABI; includes H2D of X and y,
@@ -329,12 +338,14 @@ def main():
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": wall_ms_max / args.steps, "device_ms_per_step": dev_ms_max / args.steps,
+            "device_ms_per_step_by_rank": [round(v, 1) for v in rank_ms.tolist()],
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "int64 fixed-point histograms over f32 gradients (f64 split gains)", "data": "synthetic",
             "config": describe(args.workload, args, world),
             "roofline": {
                 "bound": "hbm", "kernel": "k_hist", "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": (achieved / peak) if achieved else None, "traffic": ncu_traffic(), "peak_source": peak_src,
+                "frac_of_8tbs_spec": (achieved / 8000.0) if achieved else None,
                 "launches": hist_launches, "avg_launch_ms": hist_ms / max(hist_launches, 1),
                 "algorithmic_bytes_per_launch": hist_bytes / max(hist_launches, 1),
                 "row_features_per_s": hist_rf / (hist_ms * 1e-3) if hist_ms > 0 else None,
