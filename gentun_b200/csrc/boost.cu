@@ -51,28 +51,6 @@ __device__ __forceinline__ float split_gain(const JobParams& p, double GL, doubl
   float wl = calc_weight(p, GL, HL), wr = calc_weight(p, GR, HR);
   return gain_given_weight(p, GL, HL, wl) + gain_given_weight(p, GR, HR, wr);
 }
-// fp32 estimate of split_gain - root_gain's first two terms (same formulas, float throughout);
-// mag returns the size of the terms, from which the caller bounds the estimate's rounding error
-__device__ __forceinline__ float gain_term_est(const JobParams& p, float G, float H) {
-  // branch-free (lanes of a warp scan different features, so data-dependent branches would serialise):
-  // ThresholdL1 as G - clamp(G, -alpha, alpha); an empty side (H <= 0) contributes nothing
-  const float t = G - fminf(fmaxf(G, -p.alpha), p.alpha);
-  const float d = H + p.lambda;
-  float r;
-  if (p.mds == 0.0f) {                 // uniform across the CTA
-    r = __fdividef(t * t, d);
-  } else {
-    float w = -__fdividef(t, d);
-    w = fminf(fmaxf(w, -p.mds), p.mds);
-    r = -(2.0f * G * w + d * (w * w));
-  }
-  return H > 0.f ? r : 0.f;
-}
-__device__ __forceinline__ float split_gain_est(const JobParams& p, float GL, float HL, float GR, float HR, float& mag) {
-  const float a = gain_term_est(p, GL, HL), b = gain_term_est(p, GR, HR);
-  mag = fabsf(a) + fabsf(b);
-  return a + b;
-}
 __device__ __forceinline__ float sigmoid_x(float x) {   // upstream common::Sigmoid
   x = fminf(-x, 88.7f);
   float denom = expf(x) + 1.0f + 1e-16f;
@@ -269,8 +247,9 @@ __global__ void __launch_bounds__(256) k_plan_hist(Wave w, int level) {
     const uint32_t cnt = nodes[bnode[s2]].cnt;
     chunks[s2] = (int)((cnt + kHistRows - 1) / kHistRows);
     if (chunks[s2] < 1) chunks[s2] = 1;
-    // several CTAs, or one CTA that may flush mid-item: accumulate with atomics into a cleared histogram
-    shr[s2] = chunks[s2] > 1 || cnt > (uint32_t)kEpochRows;
+    // several CTAs build the node: they accumulate with atomics into a cleared histogram.  A node built by one
+    // CTA is owned by it: plain stores, nothing to clear.
+    shr[s2] = chunks[s2] > 1;
   }
   __syncthreads();   // s_rows initialised
   int v[3] = {chunks[0] + chunks[1], (bnode[0] >= 0) + (bnode[1] >= 0), shr[0] + shr[1]};
@@ -317,9 +296,9 @@ __device__ __forceinline__ HistEntry* node_hist(const Wave& w, const JobParams& 
   return w.hist + ((level & 1) ? jp.hist_off[1] : jp.hist_off[0]) + (size_t)(node - level_first(level)) * w.groups * (kBins * kLanes);
 }
 
-// A node with at most kEpochRows rows keeps its histogram as int32 pairs (|cell| <= rows * 2^19 < 2^31):
+// A node with at most kNarrowRows rows keeps its histogram as int32 pairs (|cell| <= rows * 2^19 < 2^31):
 // half the bytes for the deep levels, where histogram traffic dominates.  Larger nodes use int64 pairs.
-__device__ __forceinline__ bool node_narrow(uint32_t cnt) { return cnt <= (uint32_t)kEpochRows; }
+__device__ __forceinline__ bool node_narrow(uint32_t cnt) { return cnt <= (uint32_t)kNarrowRows; }
 __device__ __forceinline__ longlong2 load_cell(const HistEntry* slot, bool narrow, size_t idx) {
   if (narrow) { const int2 v = reinterpret_cast<const int2*>(slot)[idx]; return make_longlong2((long long)v.x, (long long)v.y); }
   return reinterpret_cast<const longlong2*>(slot)[idx];
@@ -409,10 +388,17 @@ __device__ __forceinline__ void hist_accumulate(const uint4 v, const int2 g2, bo
 
 // Shared partial sums are int32.  A cell can never exceed the sum of |q| over the rows the CTA has
 // accumulated since its last flush, so the CTA tracks that sum (and the hessian sum) and flushes to
-// the int64 global histogram before another epoch of kEpochRows rows could overflow.
+// the global histogram before another epoch of kEpochRows rows could overflow.
+// How a CTA's partial sums reach the node's global histogram:
+enum FlushMode {
+  kFlushAtomic,       // node shared by several CTAs: 64-bit atomic adds into cells cleared by k_hist_zero
+  kFlushStoreNarrow,  // node owned by this CTA, <= kNarrowRows rows: int32 pairs, one plain store (never flushes early)
+  kFlushStoreWide,    // node owned by this CTA, first flush: int64 pairs, plain store
+  kFlushAddWide       // node owned by this CTA, later flushes: add to what it stored before
+};
 template <int UNITS>
 __device__ __forceinline__ void hist_flush(const Wave& w, const JobParams& jp, int level, const HistItem& it, int cg, int* sh,
-                                           bool atomic, bool rezero) {
+                                           FlushMode mode, bool rezero) {
   constexpr int kThreads = UNITS == 2 ? 256 : 512;
   constexpr int kGroupsPerCta = UNITS / 2;
   HistEntry* slot = node_hist(w, jp, level, it.node);
@@ -421,12 +407,16 @@ __device__ __forceinline__ void hist_flush(const Wave& w, const JobParams& jp, i
     const int gsel = i / (kBins * kLanes), cell = i % (kBins * kLanes);
     int* pg = sh + gsel * (2 * kBins * kLanes) + cell;
     const int g = pg[0], h = pg[kBins * kLanes];
-    if (atomic) {
+    if (mode == kFlushAtomic) {
       if (g) atomicAdd(reinterpret_cast<unsigned long long*>(&slot[c0 + i].g), (unsigned long long)(long long)g);
       if (h) atomicAdd(reinterpret_cast<unsigned long long*>(&slot[c0 + i].h), (unsigned long long)(long long)h);
+    } else if (mode == kFlushStoreNarrow) {
+      reinterpret_cast<int2*>(slot)[c0 + i] = make_int2(g, h);   // cells are int32 pairs packed from the slot base
     } else {
-      // single-CTA node (<= kEpochRows rows): narrow format, cells are int32 pairs packed from the slot base
-      reinterpret_cast<int2*>(slot)[c0 + i] = make_int2(g, h);
+      longlong2* cellp = reinterpret_cast<longlong2*>(slot) + c0 + i;
+      longlong2 v = make_longlong2((long long)g, (long long)h);
+      if (mode == kFlushAddWide) { const longlong2 o = *cellp; v.x += o.x; v.y += o.y; }
+      *cellp = v;
     }
     if (rezero) { pg[0] = 0; pg[kBins * kLanes] = 0; }
   }
@@ -473,7 +463,9 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 3 : 1) k_
     const uint32_t v = sbase + (uint32_t)(unit >> 1) * (2u * kBins * kLanes * 4u) + fl * 4u;
     asm volatile("mov.u32 %0, %1;" : "=r"(cs[s]) : "r"(v));   // opaque: keep it in a register, never rematerialise
   }
-  const bool atomic_flush = it.flags & 1;
+  const bool shared_node = it.flags & 1;
+  const bool never_early = !shared_node && cnt <= (uint32_t)kNarrowRows;   // owned narrow node: the whole node fits int32
+  bool stored = false;                                                     // owned wide node: has an early flush happened
   // three-deep software pipeline: row ids two iterations ahead, bin bytes + gradients one ahead
   HistStage<UNITS> cur, nxt;
   hist_load<UNITS>(cur, row_b, rslot, bins_unit, gq, fpad);
@@ -499,17 +491,19 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 3 : 1) k_
       __syncthreads();
       // s_abs is an upper bound, in units of 64, of sum |g_q| (sum h_q) accumulated since the last flush
       const unsigned lim = (0x7fffffffu >> 6) - (((unsigned)kEpochRows << kQuantBits) >> 6) - 64u;
-      const bool must = s_abs[0] >= lim || s_abs[1] >= lim;
+      const bool must = (s_abs[0] >= lim || s_abs[1] >= lim) && !never_early;
       __syncthreads();
       if (must) {
-        hist_flush<UNITS>(w, jp, level, it, cg, sh, true, true);
+        hist_flush<UNITS>(w, jp, level, it, cg, sh, shared_node ? kFlushAtomic : stored ? kFlushAddWide : kFlushStoreWide, true);
+        stored = true;
         if (threadIdx.x < 2) s_abs[threadIdx.x] = 0u;
         __syncthreads();
       }
     }
   }
   __syncthreads();
-  hist_flush<UNITS>(w, jp, level, it, cg, sh, atomic_flush, false);
+  hist_flush<UNITS>(w, jp, level, it, cg, sh,
+                    shared_node ? kFlushAtomic : never_early ? kFlushStoreNarrow : stored ? kFlushAddWide : kFlushStoreWide, false);
 }
 
 // ------------------------------------------------------------------ X6: split enumeration
@@ -526,28 +520,76 @@ __device__ __forceinline__ bool better(float chg, int f, int b, float ochg, int 
 
 __host__ __device__ inline int scan_chunks(int groups) { return groups <= 2 ? 8 : groups <= 4 ? 4 : 2; }
 
-// Per-lane state of one child while its feature's bins are scanned.
-struct ChildScan {
-  long long Gt, Ht;        // node totals
-  float Gt_f, Ht_f;        // same, scaled, fp32
-  float root_gain;
-  long long GL, HL;        // running prefix
-  float e1, e2;            // best and second-best estimate of this lane
+// The scan runs in two stages.  Stage 1 walks the bins with an fp32 ESTIMATE of every candidate's gain and keeps, per
+// lane, the best and second-best estimate and the prefix sums at the best.  Stage 2 re-evaluates, in the
+// reference's double/float expression order, only the candidates whose estimate is within the estimate's error
+// margin of the best one.  Stage 1 is the instruction-bound part, so it works on register copies of the three
+// regularisation constants, uses a bare reciprocal, is compiled separately for max_delta_step == 0 / != 0, and
+// runs in 32-bit integers when every histogram of the pair is in the narrow (int32) format.
+struct GainK { float alpha, lambda, mds; };
+struct ChildTot { long long Gt, Ht; float root_gain; };
+struct LaneRes { float e1, e2, smax, Gt_f, Ht_f; int b1; long long GL1, HL1; };
+
+__device__ __forceinline__ float rcp_fast(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
+// fp32 estimate of one side's CalcGain (same formulas as gain_given_weight(calc_weight)), branch-free: ThresholdL1 as
+// G - clamp(G, -alpha, alpha); an empty side (H <= 0) contributes nothing
+template <bool MDS>
+__device__ __forceinline__ float gain_term_k(const GainK& k, float G, float H) {
+  const float t = G - fminf(fmaxf(G, -k.alpha), k.alpha);
+  const float d = H + k.lambda;
+  const float rd = rcp_fast(d);
+  float r;
+  if (!MDS) {
+    r = (t * t) * rd;
+  } else {
+    const float wgt = fminf(fmaxf(-(t * rd), -k.mds), k.mds);
+    r = -(2.0f * G * wgt + d * (wgt * wgt));
+  }
+  return H > 0.f ? r : 0.f;
+}
+
+template <typename T>
+struct ChildAcc {
+  T GL, HL;        // running prefix
+  T hmin, hmax;    // a candidate keeps min_child_weight on both sides  <=>  hmin <= HL <= hmax
+  T GL1, HL1;      // prefix at the best estimate
+  float Gt_f, Ht_f, e1, e2, smax;
   int b1;
-  long long GL1, HL1;      // prefix at the best estimate
-  float smax;
 };
 
-__device__ __forceinline__ void child_step(ChildScan& c, const JobParams& jp, const longlong2 e, int b, bool in_range,
-                                           long long hmin_q, float isg, float ish) {
-  c.GL += e.x; c.HL += e.y;
-  // every bin is estimated and then masked: no divergent control flow in the hot loop
-  const bool cand = in_range & ((e.x | e.y) != 0) & (c.HL >= hmin_q) & ((c.Ht - c.HL) >= hmin_q);
-  float mag;
+template <typename T>
+__device__ __forceinline__ void acc_init(ChildAcc<T>& c, const ChildTot& t, long long hmin_q, float isg, float ish, long long GL0, long long HL0) {
+  long long lo = hmin_q, hi = t.Ht - hmin_q;
+  if (sizeof(T) == 4) {   // 32-bit lanes: prefixes stay below 2^31, so an out-of-range bound just means "never a candidate"
+    lo = lo > 0x7fffffffll ? 0x7fffffffll : lo;
+    hi = hi < -1 ? -1 : hi > 0x7fffffffll ? 0x7fffffffll : hi;
+  }
+  c.GL = (T)GL0; c.HL = (T)HL0; c.hmin = (T)lo; c.hmax = (T)hi;
+  c.GL1 = 0; c.HL1 = 0; c.b1 = -1;
+  c.Gt_f = (float)t.Gt * isg; c.Ht_f = (float)t.Ht * ish;
+  c.e1 = c.e2 = -3.0e38f; c.smax = 0.f;
+}
+
+template <typename T>
+__device__ __forceinline__ void acc_result(const ChildAcc<T>& c, LaneRes& r) {
+  r.e1 = c.e1; r.e2 = c.e2; r.smax = c.smax; r.Gt_f = c.Gt_f; r.Ht_f = c.Ht_f; r.b1 = c.b1;
+  r.GL1 = (long long)c.GL1; r.HL1 = (long long)c.HL1;
+}
+
+// one bin of one child; every bin is estimated and then masked: no divergent control flow in the hot loop
+template <typename T, bool MDS>
+__device__ __forceinline__ void child_step(ChildAcc<T>& c, const GainK& k, T ex, T ey, int b, bool in_range, float isg, float ish) {
+  c.GL += ex; c.HL += ey;
+  const bool cand = in_range & ((ex | ey) != 0) & (c.HL >= c.hmin) & (c.HL <= c.hmax);
   const float gl = (float)c.GL * isg, hl = (float)c.HL * ish;
-  float est = split_gain_est(jp, gl, hl, c.Gt_f - gl, c.Ht_f - hl, mag);
-  est = cand ? est : -3.0e38f;
-  c.smax = fmaxf(c.smax, cand ? mag : 0.0f);
+  const float a = gain_term_k<MDS>(k, gl, hl), r = gain_term_k<MDS>(k, c.Gt_f - gl, c.Ht_f - hl);
+  const float est = cand ? a + r : -3.0e38f;
+  c.smax = fmaxf(c.smax, cand ? fabsf(a) + fabsf(r) : 0.0f);
   const bool top = est > c.e1;
   c.e2 = fmaxf(c.e2, fminf(c.e1, est));
   c.e1 = fmaxf(c.e1, est);
@@ -556,22 +598,153 @@ __device__ __forceinline__ void child_step(ChildScan& c, const JobParams& jp, co
   c.HL1 = top ? c.HL : c.HL1;
 }
 
-__device__ __forceinline__ void exact_candidate(Cand& best, const JobParams& jp, const ChildScan& c, long long GL, long long HL, int f, int b,
+__device__ __forceinline__ void exact_candidate(Cand& best, const JobParams& jp, const ChildTot& t, long long GL, long long HL, int f, int b,
                                                 double inv_sg, double inv_sh) {
   const double gl = (double)GL * inv_sg, hl = (double)HL * inv_sh;
-  const double gr = (double)(c.Gt - GL) * inv_sg, hr = (double)(c.Ht - HL) * inv_sh;
+  const double gr = (double)(t.Gt - GL) * inv_sg, hr = (double)(t.Ht - HL) * inv_sh;
   if (hl >= jp.mcw && hr >= jp.mcw) {
-    const float chg = split_gain(jp, gl, hl, gr, hr) - c.root_gain;
+    const float chg = split_gain(jp, gl, hl, gr, hr) - t.root_gain;
     if (!isinf(chg) && chg > best.chg) { best.chg = chg; best.f = f; best.b = b; best.GL = GL; best.HL = HL; }
   }
+}
+
+// Stage 2 for one lane and one child.  amax / smax are the child's best estimate and largest gain term over all
+// lanes (and chunks); [b_lo, hi) is the lane's bin range and (GL0, HL0) the prefix in front of it.
+__device__ __forceinline__ Cand lane_exact(const JobParams& jp, const ChildTot& t, const LaneRes& c, int side, float amax, float smax, int f,
+                                           int b_lo, int hi, long long GL0, long long HL0, const HistEntry* hbuilt, bool nar_b,
+                                           const HistEntry* hpar, bool nar_p, size_t goff, long long hmin_q, float isg, float ish,
+                                           double inv_sg, double inv_sh) {
+  Cand best{0.0f, -1, -1, 0, 0};
+  // estimate error: a few fp32 roundings on terms of size <= smax (the right-hand sums come from an fp32
+  // subtraction from the node totals), plus the root gain
+  const float margin = 3.2e-5f * (smax + fabsf(t.root_gain)) + 1e-12f;
+  // a candidate can win only with est close to the best estimate and with a positive gain (est > root gain)
+  const float cut = fmaxf(amax, t.root_gain) - 2.0f * margin;
+  if (c.e1 >= cut) {
+    if (c.e2 < cut) {
+      // the usual case: one candidate of this lane survives; evaluate it exactly from the saved prefix
+      exact_candidate(best, jp, t, c.GL1, c.HL1, f, c.b1, inv_sg, inv_sh);
+    } else {
+      // several near-ties in this lane: walk the bins again in scan order (an empty bin repeats the previous
+      // candidate, which never wins under strict >)
+      const GainK k{jp.alpha, jp.lambda, jp.mds};
+      long long GL = GL0, HL = HL0;
+      for (int b = b_lo; b < hi; ++b) {
+        longlong2 e = load_cell(hbuilt, nar_b, goff + (size_t)b * kLanes);
+        if (side == 1) { const longlong2 pe = load_cell(hpar, nar_p, goff + (size_t)b * kLanes); e.x = pe.x - e.x; e.y = pe.y - e.y; }
+        GL += e.x; HL += e.y;
+        if ((e.x != 0 || e.y != 0) && HL >= hmin_q && (t.Ht - HL) >= hmin_q) {
+          const float glf = (float)GL * isg, hlf = (float)HL * ish;
+          const float est = k.mds == 0.0f ? gain_term_k<false>(k, glf, hlf) + gain_term_k<false>(k, c.Gt_f - glf, c.Ht_f - hlf)
+                                          : gain_term_k<true>(k, glf, hlf) + gain_term_k<true>(k, c.Gt_f - glf, c.Ht_f - hlf);
+          if (est >= cut) exact_candidate(best, jp, t, GL, HL, f, b, inv_sg, inv_sh);
+        }
+      }
+    }
+  }
+  return best;
+}
+
+template <int WIDTH>
+__device__ __forceinline__ void warp_merge(Cand& best) {
+  for (int d = WIDTH; d; d >>= 1) {
+    const float ochg = __shfl_xor_sync(0xffffffffu, best.chg, d);
+    const int of = __shfl_xor_sync(0xffffffffu, best.f, d);
+    const int ob = __shfl_xor_sync(0xffffffffu, best.b, d);
+    const long long oGL = __shfl_xor_sync(0xffffffffu, best.GL, d);
+    const long long oHL = __shfl_xor_sync(0xffffffffu, best.HL, d);
+    if (better(ochg, of, ob, best.chg, best.f, best.b)) { best.chg = ochg; best.f = of; best.b = ob; best.GL = oGL; best.HL = oHL; }
+  }
+}
+
+// The evaluated node becomes a split or a leaf (CPUExpandEntry::IsValid), and a split's two children get their
+// totals, weight and gain.  Called by two lanes: sd = 0 sets up the left child and writes the node itself, sd = 1
+// the right child.
+__device__ __forceinline__ void settle_node(const JobParams& jp, int level, Node* nodes, TreeNode* tree, int node, const ChildTot& t,
+                                            const Cand& best, double inv_sg, double inv_sh, long long hmin_q, int sd) {
+  Node& nd = nodes[node];
+  const long long Gt = t.Gt, Ht = t.Ht;
+  bool valid = best.f >= 0 && best.chg > kRtEps;
+  if (valid) {
+    const double hl = (double)best.HL * inv_sh, hr = (double)(Ht - best.HL) * inv_sh;
+    if (hl == 0.0 || hr == 0.0) valid = false;
+    if (best.chg < jp.gamma) valid = false;
+  }
+  float own_leaf = nd.leaf;
+  if (level == 0) own_leaf = jp.eta * calc_weight(jp, (double)Gt * inv_sg, (double)Ht * inv_sh);
+  if (sd == 0) {
+    if (level == 0) { nd.root_gain = t.root_gain; nd.leaf = own_leaf; }
+    nd.loss_chg = best.chg;
+    if (!valid) {
+      nd.state = kLeaf;
+      tree[node] = TreeNode{own_leaf, (int16_t)-1, (uint8_t)0, (uint8_t)kLeaf};
+    } else {
+      nd.state = kSplit; nd.feat = (int16_t)best.f; nd.bin = (uint8_t)best.b;
+      tree[node] = TreeNode{0.f, (int16_t)best.f, (uint8_t)best.b, (uint8_t)kSplit};
+    }
+  }
+  if (!valid) return;
+  const long long cgq = sd == 0 ? best.GL : Gt - best.GL, chq = sd == 0 ? best.HL : Ht - best.HL;
+  // Driver::IsChildValid; in addition a child whose hessian sum is below 2 * min_child_weight has no valid
+  // candidate (both sides need H >= min_child_weight), so evaluating it could only make it a leaf: settle that now
+  // and spare its histogram, scan and partition
+  const bool can_split = hmin_q <= 0 || chq >= 2 * hmin_q;
+  const uint8_t child_state = (level + 1 < jp.max_depth && can_split) ? kOpen : kLeaf;
+  Node& chn = nodes[2 * node + 1 + sd];
+  const double g = (double)cgq * inv_sg, h = (double)chq * inv_sh;
+  chn.G = cgq; chn.H = chq;
+  chn.leaf = jp.eta * calc_weight(jp, g, h);
+  chn.root_gain = calc_gain(jp, g, h);
+  chn.loss_chg = 0.f; chn.feat = -1; chn.bin = 0; chn.state = child_state;
+  chn.begin = 0; chn.cnt = 0; chn.buf = 0;
+  tree[2 * node + 1 + sd] = TreeNode{chn.leaf, (int16_t)-1, (uint8_t)0, child_state};
+}
+
+template <typename T>
+__device__ __forceinline__ void cell_as(const longlong2 e, T& x, T& y) { x = (T)e.x; y = (T)e.y; }
+
+// Stage 1 of the chunked kernel for one lane: bins [b_lo, hi) of its feature, both children, prefix (GLx0, HLx0) in front.
+template <typename T, bool MDS>
+__device__ __forceinline__ void chunk_stage1(const GainK k, const ChildTot& tb, const ChildTot& ts, long long hmin_q, float isg, float ish,
+                                             long long GLb0, long long HLb0, long long GLs0, long long HLs0, const HistEntry* hbuilt,
+                                             bool nar_b, const HistEntry* hpar, bool nar_p, bool has_sib, size_t goff, int b_lo, int hi,
+                                             LaneRes& rb, LaneRes& rs) {
+  ChildAcc<T> cb, cs;
+  acc_init(cb, tb, hmin_q, isg, ish, GLb0, HLb0);
+  acc_init(cs, ts, hmin_q, isg, ish, GLs0, HLs0);
+  // the loop body is long and in-order, so the next bin's cells are requested before this bin is evaluated
+  longlong2 eb = make_longlong2(0, 0), pe = make_longlong2(0, 0);
+  if (b_lo < hi) {
+    eb = load_cell(hbuilt, nar_b, goff + (size_t)b_lo * kLanes);
+    if (has_sib) pe = load_cell(hpar, nar_p, goff + (size_t)b_lo * kLanes);
+  }
+  for (int b = b_lo; b < hi; ++b) {
+    longlong2 eb_n = make_longlong2(0, 0), pe_n = make_longlong2(0, 0);
+    if (b + 1 < hi) {
+      eb_n = load_cell(hbuilt, nar_b, goff + (size_t)(b + 1) * kLanes);
+      if (has_sib) pe_n = load_cell(hpar, nar_p, goff + (size_t)(b + 1) * kLanes);
+    }
+    // a bin that is empty for every feature of the warp (common in small nodes) changes no prefix and offers no
+    // candidate: skip both evaluations.  (If the parent's cell is zero, so are both children's.)
+    const bool occupied = has_sib ? ((pe.x | pe.y | eb.x | eb.y) != 0) : ((eb.x | eb.y) != 0);
+    if (__any_sync(__activemask(), occupied)) {
+      T bx, by, sx, sy;
+      cell_as(eb, bx, by);
+      cell_as(make_longlong2(pe.x - eb.x, pe.y - eb.y), sx, sy);
+      child_step<T, MDS>(cb, k, bx, by, b, true, isg, ish);
+      if (has_sib) child_step<T, MDS>(cs, k, sx, sy, b, true, isg, ish);
+    }
+    eb = eb_n; pe = pe_n;
+  }
+  acc_result(cb, rb);
+  acc_result(cs, rs);
 }
 
 // One CTA per (job, parent).  Warps = feature groups x bin chunks, lane = feature; every warp scans BOTH
 // children of the parent: the built child's cells are read once, the sibling's are formed on the fly as
 // parent - built (and stored when a later level needs them as a parent).
 // Pass 1: chunk sums.  Pass 2: with the chunk prefix from shared memory each lane runs EnumerateSplit<+1>
-// over its bins with a branch-free fp32 gain estimate; only candidates within the estimate's error
-// margin of the best one are re-evaluated in the reference's double/float expression order.
+// over its bins (stage 1 above), then stage 2.
 __device__ __forceinline__ void scan_pair(const Wave& w, int level, const PairRec pr) {
   const int j = pr.job;
   const JobState& js = w.js[j];
@@ -600,12 +773,9 @@ __device__ __forceinline__ void scan_pair(const Wave& w, int level, const PairRe
   const float isg = (float)inv_sg, ish = (float)inv_sh;
   const int b_lo = ch * CB, b_hi = min(b_lo + CB, maxnc);
 
-  ChildScan cb, cs;   // built child, sibling
-  cb.Gt = nodes[bnode].G; cb.Ht = nodes[bnode].H; cb.root_gain = nodes[bnode].root_gain;
-  cs.Gt = nodes[snode].G; cs.Ht = nodes[snode].H; cs.root_gain = nodes[snode].root_gain;
-  if (level == 0) cb.root_gain = calc_gain(jp, (double)cb.Gt * inv_sg, (double)cb.Ht * inv_sh);
-  cb.Gt_f = (float)cb.Gt * isg; cb.Ht_f = (float)cb.Ht * ish;
-  cs.Gt_f = (float)cs.Gt * isg; cs.Ht_f = (float)cs.Ht * ish;
+  ChildTot tb{nodes[bnode].G, nodes[bnode].H, nodes[bnode].root_gain};
+  const ChildTot ts{nodes[snode].G, nodes[snode].H, nodes[snode].root_gain};
+  if (level == 0) tb.root_gain = calc_gain(jp, (double)tb.Gt * inv_sg, (double)tb.Ht * inv_sh);
 
   __shared__ longlong2 s_sum[16][2][kLanes];   // chunk sums per warp: built, sibling
   __shared__ float s_est[16][4];
@@ -627,40 +797,27 @@ __device__ __forceinline__ void scan_pair(const Wave& w, int level, const PairRe
     s_sum[warp][1][lane] = as;
   }
   __syncthreads();
-  cb.GL = 0; cb.HL = 0; cs.GL = 0; cs.HL = 0;
+  long long GLb0 = 0, HLb0 = 0, GLs0 = 0, HLs0 = 0;
   for (int k = 0; k < ch; ++k) {
-    const longlong2 tb = s_sum[warp - ch + k][0][lane], ts = s_sum[warp - ch + k][1][lane];
-    cb.GL += tb.x; cb.HL += tb.y; cs.GL += ts.x; cs.HL += ts.y;
+    const longlong2 tb0 = s_sum[warp - ch + k][0][lane], ts0 = s_sum[warp - ch + k][1][lane];
+    GLb0 += tb0.x; HLb0 += tb0.y; GLs0 += ts0.x; HLs0 += ts0.y;
   }
-  const long long GLb0 = cb.GL, HLb0 = cb.HL, GLs0 = cs.GL, HLs0 = cs.HL;
   // hl >= mcw  <=>  HL_q >= mcw * sh (exact: sh is a power of two)
   const long long hmin_q = (long long)ceil((double)jp.mcw * (double)js.sh);
-  cb.e1 = cb.e2 = cs.e1 = cs.e2 = -3.0e38f; cb.b1 = cs.b1 = -1; cb.GL1 = cb.HL1 = cs.GL1 = cs.HL1 = 0; cb.smax = cs.smax = 0.f;
   const int hi = factive ? min(b_hi, nc) : b_lo;
+  LaneRes rb, rs;
   {
-    // the loop body is long and in-order, so the next bin's cells are requested before this bin is evaluated
-    longlong2 eb = make_longlong2(0, 0), pe = make_longlong2(0, 0);
-    if (b_lo < hi) {
-      eb = load_cell(hbuilt, nar_b, goff + (size_t)b_lo * kLanes);
-      if (has_sib) pe = load_cell(hpar, nar_p, goff + (size_t)b_lo * kLanes);
-    }
-    for (int b = b_lo; b < hi; ++b) {
-      longlong2 eb_n = make_longlong2(0, 0), pe_n = make_longlong2(0, 0);
-      if (b + 1 < hi) {
-        eb_n = load_cell(hbuilt, nar_b, goff + (size_t)(b + 1) * kLanes);
-        if (has_sib) pe_n = load_cell(hpar, nar_p, goff + (size_t)(b + 1) * kLanes);
-      }
-      // a bin that is empty for every feature of the warp (common in small nodes) changes no prefix and offers no
-      // candidate: skip both evaluations.  (If the parent's cell is zero, so are both children's.)
-      const bool occupied = has_sib ? ((pe.x | pe.y | eb.x | eb.y) != 0) : ((eb.x | eb.y) != 0);
-      if (__any_sync(__activemask(), occupied)) {
-        child_step(cb, jp, eb, b, true, hmin_q, isg, ish);
-        if (has_sib) child_step(cs, jp, make_longlong2(pe.x - eb.x, pe.y - eb.y), b, true, hmin_q, isg, ish);
-      }
-      eb = eb_n; pe = pe_n;
+    const GainK k{jp.alpha, jp.lambda, jp.mds};
+    const bool all32 = nar_b && (!has_sib || nar_p);   // every prefix of the pair fits 32 bits
+    if (k.mds == 0.0f) {
+      if (all32) chunk_stage1<int, false>(k, tb, ts, hmin_q, isg, ish, GLb0, HLb0, GLs0, HLs0, hbuilt, nar_b, hpar, nar_p, has_sib, goff, b_lo, hi, rb, rs);
+      else chunk_stage1<long long, false>(k, tb, ts, hmin_q, isg, ish, GLb0, HLb0, GLs0, HLs0, hbuilt, nar_b, hpar, nar_p, has_sib, goff, b_lo, hi, rb, rs);
+    } else {
+      if (all32) chunk_stage1<int, true>(k, tb, ts, hmin_q, isg, ish, GLb0, HLb0, GLs0, HLs0, hbuilt, nar_b, hpar, nar_p, has_sib, goff, b_lo, hi, rb, rs);
+      else chunk_stage1<long long, true>(k, tb, ts, hmin_q, isg, ish, GLb0, HLb0, GLs0, HLs0, hbuilt, nar_b, hpar, nar_p, has_sib, goff, b_lo, hi, rb, rs);
     }
   }
-  float v0 = cb.e1, v1 = cb.smax, v2 = cs.e1, v3 = cs.smax;
+  float v0 = rb.e1, v1 = rb.smax, v2 = rs.e1, v3 = rs.smax;
   for (int d = 16; d; d >>= 1) {
     v0 = fmaxf(v0, __shfl_xor_sync(0xffffffffu, v0, d)); v1 = fmaxf(v1, __shfl_xor_sync(0xffffffffu, v1, d));
     v2 = fmaxf(v2, __shfl_xor_sync(0xffffffffu, v2, d)); v3 = fmaxf(v3, __shfl_xor_sync(0xffffffffu, v3, d));
@@ -674,45 +831,11 @@ __device__ __forceinline__ void scan_pair(const Wave& w, int level, const PairRe
   Cand bestc[2];
 #pragma unroll
   for (int side = 0; side < 2; ++side) {
-    const ChildScan& c = side == 0 ? cb : cs;
-    const float amax = side == 0 ? v0 : v2, smax = side == 0 ? v1 : v3;
     Cand best{0.0f, -1, -1, 0, 0};
-    if (side == 0 || has_sib) {
-      // estimate error: a few fp32 roundings on terms of size <= smax (the right-hand sums come from an fp32
-      // subtraction from the node totals), plus the root gain
-      const float margin = 3.2e-5f * (smax + fabsf(c.root_gain)) + 1e-12f;
-      // a candidate can win only with est close to the best estimate and with a positive gain (est > root gain)
-      const float cut = fmaxf(amax, c.root_gain) - 2.0f * margin;
-      if (c.e1 >= cut) {
-        if (c.e2 < cut) {
-          // the usual case: one candidate of this lane survives; evaluate it exactly from the saved prefix
-          exact_candidate(best, jp, c, c.GL1, c.HL1, f, c.b1, inv_sg, inv_sh);
-        } else {
-          // several near-ties in this lane: walk the bins again in scan order (an empty bin repeats the previous
-          // candidate, which never wins under strict >)
-          long long GL = side == 0 ? GLb0 : GLs0, HL = side == 0 ? HLb0 : HLs0;
-          for (int b = b_lo; b < hi; ++b) {
-            longlong2 e = load_cell(hbuilt, nar_b, goff + (size_t)b * kLanes);
-            if (side == 1) { const longlong2 pe = load_cell(hpar, nar_p, goff + (size_t)b * kLanes); e.x = pe.x - e.x; e.y = pe.y - e.y; }
-            GL += e.x; HL += e.y;
-            if ((e.x != 0 || e.y != 0) && HL >= hmin_q && (c.Ht - HL) >= hmin_q) {
-              float mag;
-              const float glf = (float)GL * isg, hlf = (float)HL * ish;
-              const float est = split_gain_est(jp, glf, hlf, c.Gt_f - glf, c.Ht_f - hlf, mag);
-              if (est >= cut) exact_candidate(best, jp, c, GL, HL, f, b, inv_sg, inv_sh);
-            }
-          }
-        }
-      }
-    }
-    for (int d = 16; d; d >>= 1) {
-      const float ochg = __shfl_xor_sync(0xffffffffu, best.chg, d);
-      const int of = __shfl_xor_sync(0xffffffffu, best.f, d);
-      const int ob = __shfl_xor_sync(0xffffffffu, best.b, d);
-      const long long oGL = __shfl_xor_sync(0xffffffffu, best.GL, d);
-      const long long oHL = __shfl_xor_sync(0xffffffffu, best.HL, d);
-      if (better(ochg, of, ob, best.chg, best.f, best.b)) { best.chg = ochg; best.f = of; best.b = ob; best.GL = oGL; best.HL = oHL; }
-    }
+    if (side == 0 || has_sib)
+      best = lane_exact(jp, side == 0 ? tb : ts, side == 0 ? rb : rs, side, side == 0 ? v0 : v2, side == 0 ? v1 : v3, f, b_lo, hi,
+                        side == 0 ? GLb0 : GLs0, side == 0 ? HLb0 : HLs0, hbuilt, nar_b, hpar, nar_p, goff, hmin_q, isg, ish, inv_sg, inv_sh);
+    warp_merge<16>(best);
     bestc[side] = best;
   }
   if (lane == 0) { s_c[warp][0] = bestc[0]; s_c[warp][1] = bestc[1]; }
@@ -722,64 +845,215 @@ __device__ __forceinline__ void scan_pair(const Wave& w, int level, const PairRe
   const int side = warp;
   if (side > 1 || (side == 1 && !has_sib)) return;
   Cand best = lane < G * NCH ? s_c[lane][side] : Cand{0.0f, -1, -1, 0, 0};
-  for (int d = 8; d; d >>= 1) {
-    const float ochg = __shfl_xor_sync(0xffffffffu, best.chg, d);
-    const int of = __shfl_xor_sync(0xffffffffu, best.f, d);
-    const int ob = __shfl_xor_sync(0xffffffffu, best.b, d);
-    const long long oGL = __shfl_xor_sync(0xffffffffu, best.GL, d);
-    const long long oHL = __shfl_xor_sync(0xffffffffu, best.HL, d);
-    if (better(ochg, of, ob, best.chg, best.f, best.b)) { best.chg = ochg; best.f = of; best.b = ob; best.GL = oGL; best.HL = oHL; }
-  }
+  warp_merge<8>(best);
   best.chg = __shfl_sync(0xffffffffu, best.chg, 0); best.f = __shfl_sync(0xffffffffu, best.f, 0);
   best.b = __shfl_sync(0xffffffffu, best.b, 0);
   best.GL = __shfl_sync(0xffffffffu, best.GL, 0); best.HL = __shfl_sync(0xffffffffu, best.HL, 0);
   if (lane > 1) return;
-  const ChildScan& c = side == 0 ? cb : cs;
-  const int node = side == 0 ? bnode : snode;
-  const long long Gt = c.Gt, Ht = c.Ht;
-  Node& nd = nodes[node];
-  bool valid = best.f >= 0 && best.chg > kRtEps;   // CPUExpandEntry::IsValid
-  if (valid) {
-    const double hl = (double)best.HL * inv_sh, hr = (double)(Ht - best.HL) * inv_sh;
-    if (hl == 0.0 || hr == 0.0) valid = false;
-    if (best.chg < jp.gamma) valid = false;
-  }
-  float own_leaf = nd.leaf;
-  if (level == 0) own_leaf = jp.eta * calc_weight(jp, (double)Gt * inv_sg, (double)Ht * inv_sh);
-  if (lane == 0) {
-    if (level == 0) { nd.root_gain = c.root_gain; nd.leaf = own_leaf; }
-    nd.loss_chg = best.chg;
-    if (!valid) {
-      nd.state = kLeaf;
-      tree[node] = TreeNode{own_leaf, (int16_t)-1, (uint8_t)0, (uint8_t)kLeaf};
-    } else {
-      nd.state = kSplit; nd.feat = (int16_t)best.f; nd.bin = (uint8_t)best.b;
-      tree[node] = TreeNode{0.f, (int16_t)best.f, (uint8_t)best.b, (uint8_t)kSplit};
-    }
-  }
-  if (!valid) return;
-  const int sd = lane;   // lane 0: left grandchild, lane 1: right grandchild
-  const long long cgq = sd == 0 ? best.GL : Gt - best.GL, chq = sd == 0 ? best.HL : Ht - best.HL;
-  // Driver::IsChildValid; in addition a child whose hessian sum is below 2 * min_child_weight has no valid
-  // candidate (both sides need H >= min_child_weight), so evaluating it could only make it a leaf: settle that now
-  // and spare its histogram, scan and partition
-  const bool can_split = hmin_q <= 0 || chq >= 2 * hmin_q;
-  const uint8_t child_state = (level + 1 < jp.max_depth && can_split) ? kOpen : kLeaf;
-  Node& chn = nodes[2 * node + 1 + sd];
-  const double g = (double)cgq * inv_sg, h = (double)chq * inv_sh;
-  chn.G = cgq; chn.H = chq;
-  chn.leaf = jp.eta * calc_weight(jp, g, h);
-  chn.root_gain = calc_gain(jp, g, h);
-  chn.loss_chg = 0.f; chn.feat = -1; chn.bin = 0; chn.state = child_state;
-  chn.begin = 0; chn.cnt = 0; chn.buf = 0;
-  tree[2 * node + 1 + sd] = TreeNode{chn.leaf, (int16_t)-1, (uint8_t)0, child_state};
+  settle_node(jp, level, nodes, tree, side == 0 ? bnode : snode, side == 0 ? tb : ts, best, inv_sg, inv_sh, hmin_q, lane);
 }
+
+// Levels with few pairs use k_scan (a whole CTA per pair, bins split over warps); levels with at least
+// kDeepPairs pairs use k_scan_deep (one warp per pair and feature group).  Both are launched every level
+// and decide from the device-side pair count.
+#ifndef GT_DEEP_PAIRS
+#define GT_DEEP_PAIRS 1024
+#endif
+constexpr int kDeepPairs = GT_DEEP_PAIRS;
 
 __global__ void __launch_bounds__(512, 2) k_scan(Wave w, int level) {
   const int n_pairs = (int)w.counters[5 + (level & 1)];
+  if (n_pairs >= kDeepPairs) return;
   for (int pair_idx = blockIdx.x; pair_idx < n_pairs; pair_idx += gridDim.x) {
     scan_pair(w, level, w.pairs[pair_idx]);
     __syncthreads();   // shared scratch is reused by the next pair
+  }
+}
+
+// ---- the many-pairs variant.  With thousands of (job, parent) pairs in a level there is no need to split one pair's
+// bins over warps: one warp owns (pair, feature group), walks all bins of its 32 features ONCE -- sibling = parent -
+// built formed, stored and scanned in the same pass, so every histogram cell is read exactly once -- and the
+// latency of those reads is covered by a per-lane ring in shared memory filled with cp.async (kScanAhead bins
+// in flight per lane, no registers held), instead of by the one-bin register prefetch of the chunked kernel.
+#ifndef GT_SCAN_AHEAD
+#define GT_SCAN_AHEAD 4
+#endif
+#ifndef GT_DEEP_CTAS
+#define GT_DEEP_CTAS 3
+#endif
+constexpr int kScanAhead = GT_SCAN_AHEAD;
+constexpr int kScanRing = kScanAhead + 1;   // the slot refilled in an iteration is the one consumed in the previous iteration
+constexpr int kDeepWarps = 8;
+constexpr int kDeepWarpSmem = kScanRing * 2 * kLanes * 16;   // ring bytes per warp
+
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async8(uint32_t dst, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+template <typename T>
+__device__ __forceinline__ void ring_cell(const uint4 v, bool narrow, T& x, T& y) {
+  if (sizeof(T) == 4 || narrow) { x = (T)(int)v.x; y = (T)(int)v.y; return; }
+  x = (T)(long long)(((unsigned long long)v.y << 32) | v.x);
+  y = (T)(long long)(((unsigned long long)v.w << 32) | v.z);
+}
+
+struct DeepArgs {
+  const char* src_b; const char* src_p;   // this lane's first cell of the built child / the parent
+  HistEntry* hsib;
+  size_t goff;
+  int nb, hi;                             // bins to walk (the group's largest cut count); bins in which this lane's feature is a candidate
+  bool nar_b, nar_p, nar_s, has_sib, write_sib;
+};
+
+// Stage 1 of the many-pairs kernel for one lane: all bins of its feature, both children, cells through the ring.
+template <typename T, bool MDS>
+__device__ __forceinline__ void deep_stage1(const GainK k, const ChildTot& tb, const ChildTot& ts, long long hmin_q, float isg, float ish,
+                                            const DeepArgs& a, uint4* ring, uint32_t ring_s, LaneRes& rb, LaneRes& rs) {
+  ChildAcc<T> cb, cs;
+  acc_init(cb, tb, hmin_q, isg, ish, 0, 0);
+  acc_init(cs, ts, hmin_q, isg, ish, 0, 0);
+  const int nb = a.nb, hi = a.hi;
+  const bool nar_b = sizeof(T) == 4 ? true : a.nar_b, nar_p = sizeof(T) == 4 ? true : a.nar_p, has_sib = a.has_sib;
+  const unsigned step_b = kLanes * (nar_b ? 8 : 16), step_p = kLanes * (nar_p ? 8 : 16);
+  const char* src_b = a.src_b;
+  const char* src_p = a.src_p;
+  auto request = [&](int b, int slot) {
+    if (b < nb) {
+      const uint32_t dst = ring_s + (uint32_t)slot * (2 * kLanes * 16);
+      if (nar_b) cp_async8(dst, src_b + (size_t)b * step_b); else cp_async16(dst, src_b + (size_t)b * step_b);
+      if (has_sib) {
+        if (nar_p) cp_async8(dst + kLanes * 16, src_p + (size_t)b * step_p); else cp_async16(dst + kLanes * 16, src_p + (size_t)b * step_p);
+      }
+    }
+    cp_async_commit();   // a group per bin, empty past the end, so the wait below always counts the same
+  };
+#pragma unroll
+  for (int d = 0; d < kScanAhead; ++d) request(d, d);
+  int slot = 0, slot_in = kScanAhead;
+  for (int b = 0; b < nb; ++b) {
+    cp_async_wait<kScanAhead - 1>();
+    T bx, by, px = 0, py = 0;
+    ring_cell(ring[slot * (2 * kLanes)], nar_b, bx, by);
+    if (has_sib) ring_cell(ring[slot * (2 * kLanes) + kLanes], nar_p, px, py);
+    request(b + kScanAhead, slot_in);
+    slot = slot + 1 == kScanRing ? 0 : slot + 1;
+    slot_in = slot_in + 1 == kScanRing ? 0 : slot_in + 1;
+    const T sx = px - bx, sy = py - by;
+    if (a.write_sib) store_cell(a.hsib, a.nar_s, a.goff + (size_t)b * kLanes, make_longlong2((long long)sx, (long long)sy));
+    const bool occupied = has_sib ? ((px | py | bx | by) != 0) : ((bx | by) != 0);
+    if (__any_sync(0xffffffffu, occupied)) {
+      const bool in_range = b < hi;
+      child_step<T, MDS>(cb, k, bx, by, b, in_range, isg, ish);
+      if (has_sib) child_step<T, MDS>(cs, k, sx, sy, b, in_range, isg, ish);
+    }
+  }
+  acc_result(cb, rb);
+  acc_result(cs, rs);
+}
+
+// One CTA = one pair, one warp per feature group: the only barriers are between the warps of that pair, and the
+// hardware CTA scheduler balances pairs of different cost (narrow / wide cells, single children, empty bins).
+__global__ void __launch_bounds__(kDeepWarps * 32, GT_DEEP_CTAS) k_scan_deep(Wave w, int level) {
+  extern __shared__ uint4 s_ring[];                       // [warp][slot][built | parent][lane]
+  __shared__ float s_est[kDeepWarps][4];
+  __shared__ Cand s_c[kDeepWarps][2];
+  const int n_pairs = (int)w.counters[5 + (level & 1)];
+  if (n_pairs < kDeepPairs || (int)blockIdx.x >= n_pairs) return;
+  const int G = w.groups;                                  // == warps of this CTA (G <= 8 by kMaskWords)
+  const int grp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint4* ring = s_ring + (size_t)grp * (kScanRing * 2 * kLanes) + lane;
+  const uint32_t ring_s = (uint32_t)__cvta_generic_to_shared(ring);
+  const PairRec pr = w.pairs[blockIdx.x];
+  const int j = pr.job;
+  const JobState& js = w.js[j];
+  const JobParams& jp = w.jp[j];
+  Node* nodes = w.nodes + (size_t)j * kNodeCap;
+  const bool has_sib = level > 0 && !pr.single;
+  const int bnode = level == 0 ? 0 : 2 * pr.parent + 1 + pr.build_right;
+  const int snode = level == 0 ? 0 : 2 * pr.parent + 2 - pr.build_right;
+  const int f = grp * kLanes + lane;
+  const int nc = f < w.f ? w.folds[jp.fold].ncuts[f] : 0;
+  const bool factive = f < w.f && ((js.lmask[f >> 5] >> (f & 31)) & 1u);
+  const int hi = factive ? nc : 0;
+  const size_t goff = (size_t)grp * (kBins * kLanes) + lane;
+  const bool nar_b = node_narrow(nodes[bnode].cnt), nar_p = has_sib ? node_narrow(nodes[pr.parent].cnt) : false;
+  const HistEntry* hbuilt = node_hist(w, jp, level, bnode);
+  const HistEntry* hpar = has_sib ? node_hist(w, jp, level - 1, pr.parent) : nullptr;
+  const long long hmin_q = (long long)ceil((double)jp.mcw * (double)js.sh);
+  LaneRes rb, rs;
+  {
+    DeepArgs a;
+    a.has_sib = has_sib;
+    a.nb = w.grp_maxnc[jp.fold * G + grp];
+    a.hi = hi;
+    a.write_sib = has_sib && (level + 1 < jp.max_depth);
+    a.goff = goff;
+    a.nar_b = nar_b; a.nar_p = nar_p;
+    a.nar_s = node_narrow(nodes[snode].cnt);
+    a.src_b = reinterpret_cast<const char*>(hbuilt) + goff * (nar_b ? 8 : 16);
+    a.src_p = has_sib ? reinterpret_cast<const char*>(hpar) + goff * (nar_p ? 8 : 16) : nullptr;
+    a.hsib = node_hist(w, jp, level, snode);
+    const float isg = (float)js.inv_sg, ish = (float)js.inv_sh;
+    ChildTot tb{nodes[bnode].G, nodes[bnode].H, nodes[bnode].root_gain};
+    const ChildTot ts{nodes[snode].G, nodes[snode].H, nodes[snode].root_gain};
+    if (level == 0) tb.root_gain = calc_gain(jp, (double)tb.Gt * js.inv_sg, (double)tb.Ht * js.inv_sh);
+    const GainK k{jp.alpha, jp.lambda, jp.mds};
+    const bool all32 = nar_b && (!has_sib || nar_p);
+    if (k.mds == 0.0f) {
+      if (all32) deep_stage1<int, false>(k, tb, ts, hmin_q, isg, ish, a, ring, ring_s, rb, rs);
+      else deep_stage1<long long, false>(k, tb, ts, hmin_q, isg, ish, a, ring, ring_s, rb, rs);
+    } else {
+      if (all32) deep_stage1<int, true>(k, tb, ts, hmin_q, isg, ish, a, ring, ring_s, rb, rs);
+      else deep_stage1<long long, true>(k, tb, ts, hmin_q, isg, ish, a, ring, ring_s, rb, rs);
+    }
+  }
+  float v0 = rb.e1, v1 = rb.smax, v2 = rs.e1, v3 = rs.smax;
+  for (int d = 16; d; d >>= 1) {
+    v0 = fmaxf(v0, __shfl_xor_sync(0xffffffffu, v0, d)); v1 = fmaxf(v1, __shfl_xor_sync(0xffffffffu, v1, d));
+    v2 = fmaxf(v2, __shfl_xor_sync(0xffffffffu, v2, d)); v3 = fmaxf(v3, __shfl_xor_sync(0xffffffffu, v3, d));
+  }
+  if (lane == 0) { s_est[grp][0] = v0; s_est[grp][1] = v1; s_est[grp][2] = v2; s_est[grp][3] = v3; }
+  __syncthreads();
+  v0 = v2 = -3.0e38f; v1 = v3 = 0.f;
+  for (int k = 0; k < G; ++k) {
+    v0 = fmaxf(v0, s_est[k][0]); v1 = fmaxf(v1, s_est[k][1]); v2 = fmaxf(v2, s_est[k][2]); v3 = fmaxf(v3, s_est[k][3]);
+  }
+  // stage 2 and the node updates re-read the per-pair values they need: only the lane results live across the bin loop
+  const double inv_sg = js.inv_sg, inv_sh = js.inv_sh;
+  const float isg = (float)inv_sg, ish = (float)inv_sh;
+  Cand bestc[2] = {Cand{0.0f, -1, -1, 0, 0}, Cand{0.0f, -1, -1, 0, 0}};
+#pragma unroll
+  for (int side = 0; side < 2; ++side) {
+    if (side == 0 || has_sib) {
+      const int node = side == 0 ? bnode : snode;
+      ChildTot t{nodes[node].G, nodes[node].H, nodes[node].root_gain};
+      if (level == 0) t.root_gain = calc_gain(jp, (double)t.Gt * inv_sg, (double)t.Ht * inv_sh);
+      Cand best = lane_exact(jp, t, side == 0 ? rb : rs, side, side == 0 ? v0 : v2, side == 0 ? v1 : v3, f, 0, hi, 0, 0,
+                             hbuilt, nar_b, hpar, nar_p, goff, hmin_q, isg, ish, inv_sg, inv_sh);
+      warp_merge<16>(best);
+      bestc[side] = best;
+    }
+  }
+  if (lane == 0) { s_c[grp][0] = bestc[0]; s_c[grp][1] = bestc[1]; }
+  __syncthreads();
+  // the first warp finishes both children: lanes 0,1 the built child's two grandchildren, lanes 2,3 the sibling's
+  if (grp == 0 && lane < (has_sib ? 4 : 2)) {
+    const int side = lane >> 1;
+    Cand best = s_c[0][side];
+    for (int k = 1; k < G; ++k) {
+      const Cand o = s_c[k][side];
+      if (better(o.chg, o.f, o.b, best.chg, best.f, best.b)) best = o;
+    }
+    const int node = side == 0 ? bnode : snode;
+    ChildTot t{nodes[node].G, nodes[node].H, nodes[node].root_gain};
+    if (level == 0) t.root_gain = calc_gain(jp, (double)t.Gt * inv_sg, (double)t.Ht * inv_sh);
+    settle_node(jp, level, nodes, w.tree + (size_t)j * kNodeCap, node, t, best, inv_sg, inv_sh, hmin_q, lane & 1);
   }
 }
 
@@ -1080,7 +1354,9 @@ int hist_smem_bytes() { return kHistSmem; }
 int configure_kernels() {
   cudaError_t e = cudaFuncSetAttribute(k_hist<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmem);
   if (e != cudaSuccess) return (int)e;
-  return (int)cudaFuncSetAttribute(k_hist<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * kHistSmem);
+  e = cudaFuncSetAttribute(k_hist<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * kHistSmem);
+  if (e != cudaSuccess) return (int)e;
+  return (int)cudaFuncSetAttribute(k_scan_deep, cudaFuncAttributeMaxDynamicSharedMemorySize, kDeepWarps * kDeepWarpSmem);
 }
 
 void launch_init_wave(const Wave& w, cudaStream_t s) {
@@ -1102,6 +1378,7 @@ void launch_scan(const Wave& w, int level, cudaStream_t s) {
   const long long bound = (long long)w.lvl_jobs[level] * (level == 0 ? 1 : (1 << (level - 1)));
   const int grid = (int)(bound < 148 * 4 ? bound : 148 * 4);   // CTAs loop over the wave-wide pair list
   k_scan<<<grid, w.groups * scan_chunks(w.groups) * 32, 0, s>>>(w, level);
+  if (bound >= kDeepPairs) k_scan_deep<<<(unsigned)bound, w.groups * 32, w.groups * kDeepWarpSmem, s>>>(w, level);
 }
 void launch_plan_part(const Wave& w, int level, cudaStream_t s) { k_plan_part<<<w.lvl_jobs[level + 1], 256, 0, s>>>(w, level); }
 void launch_part_count(const Wave& w, int level, cudaStream_t s) {

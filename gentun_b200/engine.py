@@ -11,7 +11,7 @@ import weakref
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libgentun_b200.so")
+LIB_PATH = os.environ.get("GENTUN_B200_LIB", os.path.join(_HERE, "libgentun_b200.so"))   # override: kernel experiments only
 
 GENE_ORDER = ("eta", "min_child_weight", "max_depth", "gamma", "max_delta_step", "subsample",
               "colsample_bytree", "colsample_bylevel", "lambda", "alpha", "scale_pos_weight")
