@@ -16,6 +16,7 @@
 // does not depend on summation order.
 #include "common.cuh"
 #include "kernels.h"
+#include <cstdio>
 
 namespace gt {
 namespace {
@@ -507,6 +508,12 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 3 : 1) k_
 }
 
 // ------------------------------------------------------------------ X6: split enumeration
+#ifdef GT_SCAN_STATS   // experiment builds only: how often stage 2 takes which path
+__device__ unsigned long long g_scan_stats[4];
+#define SCAN_STAT(i, v) atomicAdd(&g_scan_stats[i], (unsigned long long)(v))
+#else
+#define SCAN_STAT(i, v)
+#endif
 struct Cand { float chg; int f; int b; long long GL, HL; };
 
 __device__ __forceinline__ bool better(float chg, int f, int b, float ochg, int of, int ob) {
@@ -528,7 +535,7 @@ __host__ __device__ inline int scan_chunks(int groups) { return groups <= 2 ? 8 
 // runs in 32-bit integers when every histogram of the pair is in the narrow (int32) format.
 struct GainK { float alpha, lambda, mds; };
 struct ChildTot { long long Gt, Ht; float root_gain; };
-struct LaneRes { float e1, e2, smax, Gt_f, Ht_f; int b1; long long GL1, HL1; };
+struct LaneRes { float e1, e2, Gt_f, Ht_f; int b1; long long GL1, HL1; };
 
 __device__ __forceinline__ float rcp_fast(float x) {
   float r;
@@ -536,60 +543,66 @@ __device__ __forceinline__ float rcp_fast(float x) {
   return r;
 }
 
-// fp32 estimate of one side's CalcGain (same formulas as gain_given_weight(calc_weight)), branch-free: ThresholdL1 as
-// G - clamp(G, -alpha, alpha); an empty side (H <= 0) contributes nothing
+// fp32 estimate of one side's CalcGain (same formulas as gain_given_weight(calc_weight)) from the side's gradient sum
+// G and its denominator d = H + lambda, branch-free: ThresholdL1 as G - clamp(G, -alpha, alpha).  Never negative.
 template <bool MDS>
-__device__ __forceinline__ float gain_term_k(const GainK& k, float G, float H) {
+__device__ __forceinline__ float gain_term_k(const GainK& k, float G, float d) {
   const float t = G - fminf(fmaxf(G, -k.alpha), k.alpha);
-  const float d = H + k.lambda;
   const float rd = rcp_fast(d);
-  float r;
-  if (!MDS) {
-    r = (t * t) * rd;
-  } else {
-    const float wgt = fminf(fmaxf(-(t * rd), -k.mds), k.mds);
-    r = -(2.0f * G * wgt + d * (wgt * wgt));
-  }
-  return H > 0.f ? r : 0.f;
+  if (!MDS) return (t * t) * rd;
+  const float wgt = fminf(fmaxf(-(t * rd), -k.mds), k.mds);
+  return -(2.0f * G * wgt + d * (wgt * wgt));
+}
+// estimate of a candidate from real-valued prefix sums (stage 2's re-walks); an empty side (H <= 0) contributes nothing
+template <bool MDS>
+__device__ __forceinline__ float split_est(const GainK& k, float gl, float hl, float gr, float hr) {
+  const float a = hl > 0.f ? gain_term_k<MDS>(k, gl, hl + k.lambda) : 0.f;
+  const float r = hr > 0.f ? gain_term_k<MDS>(k, gr, hr + k.lambda) : 0.f;
+  return a + r;
 }
 
 template <typename T>
 struct ChildAcc {
   T GL, HL;        // running prefix
   T hmin, hmax;    // a candidate keeps min_child_weight on both sides  <=>  hmin <= HL <= hmax
+  T Ht;            // node total: the right side is empty  <=>  HL == Ht
   T GL1, HL1;      // prefix at the best estimate
-  float Gt_f, Ht_f, e1, e2, smax;
+  float Gt_f, Ht_f, Htl_f, e1, e2;   // Htl_f = Ht_f + lambda
   int b1;
 };
 
 template <typename T>
-__device__ __forceinline__ void acc_init(ChildAcc<T>& c, const ChildTot& t, long long hmin_q, float isg, float ish, long long GL0, long long HL0) {
+__device__ __forceinline__ void acc_init(ChildAcc<T>& c, const ChildTot& t, const GainK& k, long long hmin_q, float isg, float ish,
+                                         long long GL0, long long HL0) {
   long long lo = hmin_q, hi = t.Ht - hmin_q;
   if (sizeof(T) == 4) {   // 32-bit lanes: prefixes stay below 2^31, so an out-of-range bound just means "never a candidate"
     lo = lo > 0x7fffffffll ? 0x7fffffffll : lo;
     hi = hi < -1 ? -1 : hi > 0x7fffffffll ? 0x7fffffffll : hi;
   }
-  c.GL = (T)GL0; c.HL = (T)HL0; c.hmin = (T)lo; c.hmax = (T)hi;
+  c.GL = (T)GL0; c.HL = (T)HL0; c.hmin = (T)lo; c.hmax = (T)hi; c.Ht = (T)t.Ht;
   c.GL1 = 0; c.HL1 = 0; c.b1 = -1;
-  c.Gt_f = (float)t.Gt * isg; c.Ht_f = (float)t.Ht * ish;
-  c.e1 = c.e2 = -3.0e38f; c.smax = 0.f;
+  c.Gt_f = (float)t.Gt * isg; c.Ht_f = (float)t.Ht * ish; c.Htl_f = c.Ht_f + k.lambda;
+  c.e1 = c.e2 = -3.0e38f;
 }
 
 template <typename T>
 __device__ __forceinline__ void acc_result(const ChildAcc<T>& c, LaneRes& r) {
-  r.e1 = c.e1; r.e2 = c.e2; r.smax = c.smax; r.Gt_f = c.Gt_f; r.Ht_f = c.Ht_f; r.b1 = c.b1;
+  r.e1 = c.e1; r.e2 = c.e2; r.Gt_f = c.Gt_f; r.Ht_f = c.Ht_f; r.b1 = c.b1;
   r.GL1 = (long long)c.GL1; r.HL1 = (long long)c.HL1;
 }
 
-// one bin of one child; every bin is estimated and then masked: no divergent control flow in the hot loop
+// one bin of one child; every bin is estimated and then masked: no divergent control flow in the hot loop.
+// (The estimate may contract multiplies and adds -- only the exact stage mirrors the reference's expression order.)
 template <typename T, bool MDS>
 __device__ __forceinline__ void child_step(ChildAcc<T>& c, const GainK& k, T ex, T ey, int b, bool in_range, float isg, float ish) {
   c.GL += ex; c.HL += ey;
   const bool cand = in_range & ((ex | ey) != 0) & (c.HL >= c.hmin) & (c.HL <= c.hmax);
-  const float gl = (float)c.GL * isg, hl = (float)c.HL * ish;
-  const float a = gain_term_k<MDS>(k, gl, hl), r = gain_term_k<MDS>(k, c.Gt_f - gl, c.Ht_f - hl);
+  const float glq = (float)c.GL, hlq = (float)c.HL;
+  const float gl = glq * isg, gr = __fmaf_rn(-glq, isg, c.Gt_f);
+  const float dl = __fmaf_rn(hlq, ish, k.lambda), dr = __fmaf_rn(-hlq, ish, c.Htl_f);
+  const float a = c.HL > 0 ? gain_term_k<MDS>(k, gl, dl) : 0.f;
+  const float r = c.HL < c.Ht ? gain_term_k<MDS>(k, gr, dr) : 0.f;
   const float est = cand ? a + r : -3.0e38f;
-  c.smax = fmaxf(c.smax, cand ? fabsf(a) + fabsf(r) : 0.0f);
   const bool top = est > c.e1;
   c.e2 = fmaxf(c.e2, fminf(c.e1, est));
   c.e1 = fmaxf(c.e1, est);
@@ -608,43 +621,6 @@ __device__ __forceinline__ void exact_candidate(Cand& best, const JobParams& jp,
   }
 }
 
-// Stage 2 for one lane and one child.  amax / smax are the child's best estimate and largest gain term over all
-// lanes (and chunks); [b_lo, hi) is the lane's bin range and (GL0, HL0) the prefix in front of it.
-__device__ __forceinline__ Cand lane_exact(const JobParams& jp, const ChildTot& t, const LaneRes& c, int side, float amax, float smax, int f,
-                                           int b_lo, int hi, long long GL0, long long HL0, const HistEntry* hbuilt, bool nar_b,
-                                           const HistEntry* hpar, bool nar_p, size_t goff, long long hmin_q, float isg, float ish,
-                                           double inv_sg, double inv_sh) {
-  Cand best{0.0f, -1, -1, 0, 0};
-  // estimate error: a few fp32 roundings on terms of size <= smax (the right-hand sums come from an fp32
-  // subtraction from the node totals), plus the root gain
-  const float margin = 3.2e-5f * (smax + fabsf(t.root_gain)) + 1e-12f;
-  // a candidate can win only with est close to the best estimate and with a positive gain (est > root gain)
-  const float cut = fmaxf(amax, t.root_gain) - 2.0f * margin;
-  if (c.e1 >= cut) {
-    if (c.e2 < cut) {
-      // the usual case: one candidate of this lane survives; evaluate it exactly from the saved prefix
-      exact_candidate(best, jp, t, c.GL1, c.HL1, f, c.b1, inv_sg, inv_sh);
-    } else {
-      // several near-ties in this lane: walk the bins again in scan order (an empty bin repeats the previous
-      // candidate, which never wins under strict >)
-      const GainK k{jp.alpha, jp.lambda, jp.mds};
-      long long GL = GL0, HL = HL0;
-      for (int b = b_lo; b < hi; ++b) {
-        longlong2 e = load_cell(hbuilt, nar_b, goff + (size_t)b * kLanes);
-        if (side == 1) { const longlong2 pe = load_cell(hpar, nar_p, goff + (size_t)b * kLanes); e.x = pe.x - e.x; e.y = pe.y - e.y; }
-        GL += e.x; HL += e.y;
-        if ((e.x != 0 || e.y != 0) && HL >= hmin_q && (t.Ht - HL) >= hmin_q) {
-          const float glf = (float)GL * isg, hlf = (float)HL * ish;
-          const float est = k.mds == 0.0f ? gain_term_k<false>(k, glf, hlf) + gain_term_k<false>(k, c.Gt_f - glf, c.Ht_f - hlf)
-                                          : gain_term_k<true>(k, glf, hlf) + gain_term_k<true>(k, c.Gt_f - glf, c.Ht_f - hlf);
-          if (est >= cut) exact_candidate(best, jp, t, GL, HL, f, b, inv_sg, inv_sh);
-        }
-      }
-    }
-  }
-  return best;
-}
-
 template <int WIDTH>
 __device__ __forceinline__ void warp_merge(Cand& best) {
   for (int d = WIDTH; d; d >>= 1) {
@@ -655,6 +631,106 @@ __device__ __forceinline__ void warp_merge(Cand& best) {
     const long long oHL = __shfl_xor_sync(0xffffffffu, best.HL, d);
     if (better(ochg, of, ob, best.chg, best.f, best.b)) { best.chg = ochg; best.f = of; best.b = ob; best.GL = oGL; best.HL = oHL; }
   }
+}
+
+// Stage 2, slow path: several candidates of ONE feature column (feature f_col, cells at goff_col) have estimates within
+// the margin of the best.  The whole warp takes the column: lane i re-reads bins b_lo + i, b_lo + 32 + i, ..., a warp
+// scan rebuilds the exact prefixes, and every candidate whose estimate reaches `cut` is evaluated exactly.  All
+// arguments are warp-uniform.  Equal gains keep the earlier bin, as the sequential scan would.
+__device__ __noinline__ Cand column_exact(const JobParams& jp, const ChildTot& t, float Gt_f, float Ht_f, int side, float cut, int f_col,
+                                             int b_lo, int hi, long long GL0, long long HL0, const HistEntry* hbuilt, bool nar_b,
+                                             const HistEntry* hpar, bool nar_p, size_t goff_col, long long hmin_q, float isg, float ish,
+                                             double inv_sg, double inv_sh) {
+  const int lane = threadIdx.x & 31;
+  const GainK k{jp.alpha, jp.lambda, jp.mds};
+  constexpr int kBlocks = kBins / 32;
+  longlong2 e[kBlocks];
+#pragma unroll
+  for (int q = 0; q < kBlocks; ++q) {
+    const int b = b_lo + q * 32 + lane;
+    e[q] = make_longlong2(0, 0);
+    if (b < hi) {
+      e[q] = load_cell(hbuilt, nar_b, goff_col + (size_t)b * kLanes);
+      if (side == 1) { const longlong2 pe = load_cell(hpar, nar_p, goff_col + (size_t)b * kLanes); e[q].x = pe.x - e[q].x; e[q].y = pe.y - e[q].y; }
+    }
+  }
+  Cand best{0.0f, -1, -1, 0, 0};
+  long long GLc = GL0, HLc = HL0;
+#pragma unroll
+  for (int q = 0; q < kBlocks; ++q) {
+    if (b_lo + q * 32 < hi) {   // warp-uniform
+      long long pg = e[q].x, ph = e[q].y;
+      for (int d = 1; d < 32; d <<= 1) {
+        const long long og = __shfl_up_sync(0xffffffffu, pg, d), oh = __shfl_up_sync(0xffffffffu, ph, d);
+        if (lane >= d) { pg += og; ph += oh; }
+      }
+      const long long GL = GLc + pg, HL = HLc + ph;
+      const int b = b_lo + q * 32 + lane;
+      if (b < hi && (e[q].x != 0 || e[q].y != 0) && HL >= hmin_q && (t.Ht - HL) >= hmin_q) {
+        const float glf = (float)GL * isg, hlf = (float)HL * ish;
+        const float est = k.mds == 0.0f ? split_est<false>(k, glf, hlf, Gt_f - glf, Ht_f - hlf) : split_est<true>(k, glf, hlf, Gt_f - glf, Ht_f - hlf);
+        if (est >= cut) exact_candidate(best, jp, t, GL, HL, f_col, b, inv_sg, inv_sh);
+      }
+      GLc += __shfl_sync(0xffffffffu, pg, 31);
+      HLc += __shfl_sync(0xffffffffu, ph, 31);
+    }
+  }
+  warp_merge<16>(best);
+  return best;
+}
+
+// Stage 2 for one child, called by all 32 lanes of a warp.  amax is the child's best estimate over (at least) this warp's
+// lanes; [b_lo, hi) is the lane's bin range and (GL0, HL0) the prefix in front
+// of it.  Returns the lane's exact best candidate.
+template <bool COOP>
+__device__ __forceinline__ Cand lane_exact(const JobParams& jp, const ChildTot& t, const LaneRes& c, int side, float amax, int f,
+                                           int b_lo, int hi, long long GL0, long long HL0, const HistEntry* hbuilt, bool nar_b,
+                                           const HistEntry* hpar, bool nar_p, size_t goff, long long hmin_q, float isg, float ish,
+                                           double inv_sg, double inv_sh) {
+  const int lane = threadIdx.x & 31;
+  Cand best{0.0f, -1, -1, 0, 0};
+  // estimate error: a few fp32 roundings on its two terms (the right-hand sums come from an fp32 subtraction from
+  // the node totals), plus the root gain.  Both terms are >= 0, so no candidate's terms exceed the best estimate.
+  const float margin = 3.2e-5f * (fmaxf(amax, 0.f) + fabsf(t.root_gain)) + 1e-12f;
+  // a candidate can win only with est close to the best estimate and with a positive gain (est > root gain)
+  const float cut = fmaxf(amax, t.root_gain) - 2.0f * margin;
+  const bool alive = c.e1 >= cut;
+  if (lane == 0) SCAN_STAT(0, 1);
+  SCAN_STAT(1, alive ? 1 : 0);
+  // the usual case: one candidate of this lane survives; evaluate it exactly from the saved prefix
+  if (alive && c.e2 < cut) exact_candidate(best, jp, t, c.GL1, c.HL1, f, c.b1, inv_sg, inv_sh);
+  if (COOP) {
+    // several near-ties in a lane: the warp re-walks that lane's column together (256 bins per lane in the many-pairs
+    // kernel: a per-lane walk would leave the pair's other warp waiting for tens of microseconds)
+    unsigned walk = __ballot_sync(0xffffffffu, alive && c.e2 >= cut);
+    while (walk) {
+      const int src = __ffs(walk) - 1;
+      if (lane == 0) SCAN_STAT(2, 1);
+      walk &= walk - 1;
+      const int hi_s = __shfl_sync(0xffffffffu, hi, src);
+      const long long GL0_s = __shfl_sync(0xffffffffu, GL0, src), HL0_s = __shfl_sync(0xffffffffu, HL0, src);
+      const Cand col = column_exact(jp, t, c.Gt_f, c.Ht_f, side, cut, f - lane + src, b_lo, hi_s, GL0_s, HL0_s, hbuilt, nar_b, hpar, nar_p,
+                                    goff - (size_t)lane + (size_t)src, hmin_q, isg, ish, inv_sg, inv_sh);
+      if (lane == src) best = col;
+    }
+  } else if (alive && c.e2 >= cut) {
+    // several near-ties in this lane: walk its (at most 128) bins again in scan order (an empty bin repeats the
+    // previous candidate, which never wins under strict >)
+    const GainK k{jp.alpha, jp.lambda, jp.mds};
+    long long GL = GL0, HL = HL0;
+    for (int b = b_lo; b < hi; ++b) {
+      longlong2 e = load_cell(hbuilt, nar_b, goff + (size_t)b * kLanes);
+      if (side == 1) { const longlong2 pe = load_cell(hpar, nar_p, goff + (size_t)b * kLanes); e.x = pe.x - e.x; e.y = pe.y - e.y; }
+      GL += e.x; HL += e.y;
+      if ((e.x != 0 || e.y != 0) && HL >= hmin_q && (t.Ht - HL) >= hmin_q) {
+        const float glf = (float)GL * isg, hlf = (float)HL * ish;
+        const float est = k.mds == 0.0f ? split_est<false>(k, glf, hlf, c.Gt_f - glf, c.Ht_f - hlf)
+                                        : split_est<true>(k, glf, hlf, c.Gt_f - glf, c.Ht_f - hlf);
+        if (est >= cut) exact_candidate(best, jp, t, GL, HL, f, b, inv_sg, inv_sh);
+      }
+    }
+  }
+  return best;
 }
 
 // The evaluated node becomes a split or a leaf (CPUExpandEntry::IsValid), and a split's two children get their
@@ -700,18 +776,121 @@ __device__ __forceinline__ void settle_node(const JobParams& jp, int level, Node
   tree[2 * node + 1 + sd] = TreeNode{chn.leaf, (int16_t)-1, (uint8_t)0, child_state};
 }
 
+// ---- stage 1 proper.  A lane walks the bins [b0, b1) of its feature for both children of a pair.  The latency of
+// the histogram reads is covered by a per-lane ring in shared memory filled with cp.async (kScanAhead bins in
+// flight per lane, no registers held); sibling = parent - built is formed, stored and scanned in the same step.
+#ifndef GT_SCAN_AHEAD
+#define GT_SCAN_AHEAD 3
+#endif
+#ifndef GT_DEEP_CTAS
+#define GT_DEEP_CTAS 2
+#endif
+#ifndef GT_SCAN_CTAS
+#define GT_SCAN_CTAS 2
+#endif
+constexpr int kScanAhead = GT_SCAN_AHEAD;
+constexpr int kScanRing = kScanAhead + 1;   // the slot refilled in an iteration is the one consumed in the previous iteration
+static_assert((kScanRing & (kScanRing - 1)) == 0, "ring slots are addressed with a mask");
+constexpr int kRingWarpBytes = kScanRing * 2 * kLanes * 16;   // [slot][built | parent][lane] 16-byte cells
+
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async8(uint32_t dst, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+template <typename T>
+__device__ __forceinline__ void ring_cell(const uint4 v, bool narrow, T& x, T& y) {
+  if (sizeof(T) == 4 || narrow) { x = (T)(int)v.x; y = (T)(int)v.y; return; }
+  x = (T)(long long)(((unsigned long long)v.y << 32) | v.x);
+  y = (T)(long long)(((unsigned long long)v.w << 32) | v.z);
+}
+
+struct WalkArgs {
+  const char* src_b; const char* src_p;   // this lane's bin-0 cell of the built child / the parent
+  HistEntry* hsib;
+  size_t goff;
+  int b0, b1, hi;                         // bins to walk (warp-uniform); this lane's feature is a candidate in bins < hi
+  long long GLb0, HLb0, GLs0, HLs0;       // prefix in front of b0: built child, sibling
+  bool nar_b, nar_p, nar_s, has_sib, write_sib;
+};
+
+template <typename T, bool MDS>
+__device__ __forceinline__ void walk_stage1(const GainK k, const ChildTot& tb, const ChildTot& ts, long long hmin_q, float isg, float ish,
+                                            const WalkArgs& a, uint4* ring, uint32_t ring_s, LaneRes& rb, LaneRes& rs) {
+  ChildAcc<T> cb, cs;
+  acc_init(cb, tb, k, hmin_q, isg, ish, a.GLb0, a.HLb0);
+  acc_init(cs, ts, k, hmin_q, isg, ish, a.GLs0, a.HLs0);
+  const int b0 = a.b0, b1 = a.b1, hi = a.hi;
+  const bool nar_b = sizeof(T) == 4 ? true : a.nar_b, nar_p = sizeof(T) == 4 ? true : a.nar_p, has_sib = a.has_sib;
+  const unsigned step_b = kLanes * (nar_b ? 8 : 16), step_p = kLanes * (nar_p ? 8 : 16);
+  const char* src_b = a.src_b;
+  const char* src_p = a.src_p;
+  auto request = [&](int b, int slot) {
+    if (b < b1) {
+      const uint32_t dst = ring_s + (uint32_t)slot * (2 * kLanes * 16);
+      if (nar_b) cp_async8(dst, src_b + (size_t)b * step_b); else cp_async16(dst, src_b + (size_t)b * step_b);
+      if (has_sib) {
+        if (nar_p) cp_async8(dst + kLanes * 16, src_p + (size_t)b * step_p); else cp_async16(dst + kLanes * 16, src_p + (size_t)b * step_p);
+      }
+    }
+    cp_async_commit();   // a group per bin, empty past the end, so the wait below always counts the same
+  };
+#pragma unroll
+  for (int d = 0; d < kScanAhead; ++d) request(b0 + d, d);
+  for (int b = b0, n = 0; b < b1; ++b, ++n) {
+    const int slot = n & (kScanRing - 1), slot_in = (n + kScanAhead) & (kScanRing - 1);
+    cp_async_wait<kScanAhead - 1>();
+    T bx, by, px = 0, py = 0;
+    ring_cell(ring[slot * (2 * kLanes)], nar_b, bx, by);
+    if (has_sib) ring_cell(ring[slot * (2 * kLanes) + kLanes], nar_p, px, py);
+    request(b + kScanAhead, slot_in);
+    const T sx = px - bx, sy = py - by;
+    if (a.write_sib) store_cell(a.hsib, a.nar_s, a.goff + (size_t)b * kLanes, make_longlong2((long long)sx, (long long)sy));
+    // a bin that is empty for every feature of the warp (common in small nodes) changes no prefix and offers no
+    // candidate: skip both evaluations.  (If the parent's cell is zero, so are both children's.)
+    const bool occupied = has_sib ? ((px | py | bx | by) != 0) : ((bx | by) != 0);
+    if (__any_sync(0xffffffffu, occupied)) {
+      const bool in_range = b < hi;
+      child_step<T, MDS>(cb, k, bx, by, b, in_range, isg, ish);
+      if (has_sib) child_step<T, MDS>(cs, k, sx, sy, b, in_range, isg, ish);
+    }
+  }
+  cp_async_wait<0>();
+  acc_result(cb, rb);
+  acc_result(cs, rs);
+}
+
+__device__ __forceinline__ void walk_dispatch(const GainK k, const ChildTot& tb, const ChildTot& ts, long long hmin_q, float isg, float ish,
+                                              const WalkArgs& a, uint4* ring, uint32_t ring_s, LaneRes& rb, LaneRes& rs) {
+  const bool all32 = a.nar_b && (!a.has_sib || a.nar_p);   // every prefix of the pair fits 32 bits
+  if (k.mds == 0.0f) {
+    if (all32) walk_stage1<int, false>(k, tb, ts, hmin_q, isg, ish, a, ring, ring_s, rb, rs);
+    else walk_stage1<long long, false>(k, tb, ts, hmin_q, isg, ish, a, ring, ring_s, rb, rs);
+  } else {
+    if (all32) walk_stage1<int, true>(k, tb, ts, hmin_q, isg, ish, a, ring, ring_s, rb, rs);
+    else walk_stage1<long long, true>(k, tb, ts, hmin_q, isg, ish, a, ring, ring_s, rb, rs);
+  }
+}
+
 template <typename T>
 __device__ __forceinline__ void cell_as(const longlong2 e, T& x, T& y) { x = (T)e.x; y = (T)e.y; }
 
-// Stage 1 of the chunked kernel for one lane: bins [b_lo, hi) of its feature, both children, prefix (GLx0, HLx0) in front.
+// Stage 1 of the chunked kernel for one lane: bins [b_lo, hi) of its feature, both children, prefix (GLx0, HLx0) in
+// front.  A chunk is at most 128 bins and the CTA runs at full occupancy, so a one-bin register prefetch is enough here
+// (the shared-memory ring of walk_stage1 was measured slower in this kernel: it costs the second resident CTA).
 template <typename T, bool MDS>
 __device__ __forceinline__ void chunk_stage1(const GainK k, const ChildTot& tb, const ChildTot& ts, long long hmin_q, float isg, float ish,
                                              long long GLb0, long long HLb0, long long GLs0, long long HLs0, const HistEntry* hbuilt,
                                              bool nar_b, const HistEntry* hpar, bool nar_p, bool has_sib, size_t goff, int b_lo, int hi,
                                              LaneRes& rb, LaneRes& rs) {
   ChildAcc<T> cb, cs;
-  acc_init(cb, tb, hmin_q, isg, ish, GLb0, HLb0);
-  acc_init(cs, ts, hmin_q, isg, ish, GLs0, HLs0);
+  acc_init(cb, tb, k, hmin_q, isg, ish, GLb0, HLb0);
+  acc_init(cs, ts, k, hmin_q, isg, ish, GLs0, HLs0);
   // the loop body is long and in-order, so the next bin's cells are requested before this bin is evaluated
   longlong2 eb = make_longlong2(0, 0), pe = make_longlong2(0, 0);
   if (b_lo < hi) {
@@ -778,7 +957,7 @@ __device__ __forceinline__ void scan_pair(const Wave& w, int level, const PairRe
   if (level == 0) tb.root_gain = calc_gain(jp, (double)tb.Gt * inv_sg, (double)tb.Ht * inv_sh);
 
   __shared__ longlong2 s_sum[16][2][kLanes];   // chunk sums per warp: built, sibling
-  __shared__ float s_est[16][4];
+  __shared__ float s_est[16][2];
   __shared__ Cand s_c[16][2];
   {
     longlong2 ab = make_longlong2(0, 0), as = make_longlong2(0, 0);
@@ -817,23 +996,20 @@ __device__ __forceinline__ void scan_pair(const Wave& w, int level, const PairRe
       else chunk_stage1<long long, true>(k, tb, ts, hmin_q, isg, ish, GLb0, HLb0, GLs0, HLs0, hbuilt, nar_b, hpar, nar_p, has_sib, goff, b_lo, hi, rb, rs);
     }
   }
-  float v0 = rb.e1, v1 = rb.smax, v2 = rs.e1, v3 = rs.smax;
+  float v0 = rb.e1, v2 = rs.e1;
   for (int d = 16; d; d >>= 1) {
-    v0 = fmaxf(v0, __shfl_xor_sync(0xffffffffu, v0, d)); v1 = fmaxf(v1, __shfl_xor_sync(0xffffffffu, v1, d));
-    v2 = fmaxf(v2, __shfl_xor_sync(0xffffffffu, v2, d)); v3 = fmaxf(v3, __shfl_xor_sync(0xffffffffu, v3, d));
+    v0 = fmaxf(v0, __shfl_xor_sync(0xffffffffu, v0, d)); v2 = fmaxf(v2, __shfl_xor_sync(0xffffffffu, v2, d));
   }
-  if (lane == 0) { s_est[warp][0] = v0; s_est[warp][1] = v1; s_est[warp][2] = v2; s_est[warp][3] = v3; }
+  if (lane == 0) { s_est[warp][0] = v0; s_est[warp][1] = v2; }
   __syncthreads();
-  v0 = v2 = -3.0e38f; v1 = v3 = 0.f;
-  for (int k = 0; k < G * NCH; ++k) {
-    v0 = fmaxf(v0, s_est[k][0]); v1 = fmaxf(v1, s_est[k][1]); v2 = fmaxf(v2, s_est[k][2]); v3 = fmaxf(v3, s_est[k][3]);
-  }
+  v0 = v2 = -3.0e38f;
+  for (int k = 0; k < G * NCH; ++k) { v0 = fmaxf(v0, s_est[k][0]); v2 = fmaxf(v2, s_est[k][1]); }
   Cand bestc[2];
 #pragma unroll
   for (int side = 0; side < 2; ++side) {
     Cand best{0.0f, -1, -1, 0, 0};
     if (side == 0 || has_sib)
-      best = lane_exact(jp, side == 0 ? tb : ts, side == 0 ? rb : rs, side, side == 0 ? v0 : v2, side == 0 ? v1 : v3, f, b_lo, hi,
+      best = lane_exact<false>(jp, side == 0 ? tb : ts, side == 0 ? rb : rs, side, side == 0 ? v0 : v2, f, b_lo, hi,
                         side == 0 ? GLb0 : GLs0, side == 0 ? HLb0 : HLs0, hbuilt, nar_b, hpar, nar_p, goff, hmin_q, isg, ish, inv_sg, inv_sh);
     warp_merge<16>(best);
     bestc[side] = best;
@@ -857,11 +1033,11 @@ __device__ __forceinline__ void scan_pair(const Wave& w, int level, const PairRe
 // kDeepPairs pairs use k_scan_deep (one warp per pair and feature group).  Both are launched every level
 // and decide from the device-side pair count.
 #ifndef GT_DEEP_PAIRS
-#define GT_DEEP_PAIRS 1024
+#define GT_DEEP_PAIRS 3072
 #endif
 constexpr int kDeepPairs = GT_DEEP_PAIRS;
 
-__global__ void __launch_bounds__(512, 2) k_scan(Wave w, int level) {
+__global__ void __launch_bounds__(512, GT_SCAN_CTAS) k_scan(Wave w, int level) {
   const int n_pairs = (int)w.counters[5 + (level & 1)];
   if (n_pairs >= kDeepPairs) return;
   for (int pair_idx = blockIdx.x; pair_idx < n_pairs; pair_idx += gridDim.x) {
@@ -871,103 +1047,19 @@ __global__ void __launch_bounds__(512, 2) k_scan(Wave w, int level) {
 }
 
 // ---- the many-pairs variant.  With thousands of (job, parent) pairs in a level there is no need to split one pair's
-// bins over warps: one warp owns (pair, feature group), walks all bins of its 32 features ONCE -- sibling = parent -
-// built formed, stored and scanned in the same pass, so every histogram cell is read exactly once -- and the
-// latency of those reads is covered by a per-lane ring in shared memory filled with cp.async (kScanAhead bins
-// in flight per lane, no registers held), instead of by the one-bin register prefetch of the chunked kernel.
-#ifndef GT_SCAN_AHEAD
-#define GT_SCAN_AHEAD 4
-#endif
-#ifndef GT_DEEP_CTAS
-#define GT_DEEP_CTAS 3
-#endif
-constexpr int kScanAhead = GT_SCAN_AHEAD;
-constexpr int kScanRing = kScanAhead + 1;   // the slot refilled in an iteration is the one consumed in the previous iteration
+// bins over warps: one warp owns (pair, feature group) and walks all bins of its 32 features ONCE, so every
+// histogram cell is read exactly once and no chunk sums are needed.
 constexpr int kDeepWarps = 8;
-constexpr int kDeepWarpSmem = kScanRing * 2 * kLanes * 16;   // ring bytes per warp
-
-__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
-}
-__device__ __forceinline__ void cp_async8(uint32_t dst, const void* src) {
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-
-template <typename T>
-__device__ __forceinline__ void ring_cell(const uint4 v, bool narrow, T& x, T& y) {
-  if (sizeof(T) == 4 || narrow) { x = (T)(int)v.x; y = (T)(int)v.y; return; }
-  x = (T)(long long)(((unsigned long long)v.y << 32) | v.x);
-  y = (T)(long long)(((unsigned long long)v.w << 32) | v.z);
-}
-
-struct DeepArgs {
-  const char* src_b; const char* src_p;   // this lane's first cell of the built child / the parent
-  HistEntry* hsib;
-  size_t goff;
-  int nb, hi;                             // bins to walk (the group's largest cut count); bins in which this lane's feature is a candidate
-  bool nar_b, nar_p, nar_s, has_sib, write_sib;
-};
-
-// Stage 1 of the many-pairs kernel for one lane: all bins of its feature, both children, cells through the ring.
-template <typename T, bool MDS>
-__device__ __forceinline__ void deep_stage1(const GainK k, const ChildTot& tb, const ChildTot& ts, long long hmin_q, float isg, float ish,
-                                            const DeepArgs& a, uint4* ring, uint32_t ring_s, LaneRes& rb, LaneRes& rs) {
-  ChildAcc<T> cb, cs;
-  acc_init(cb, tb, hmin_q, isg, ish, 0, 0);
-  acc_init(cs, ts, hmin_q, isg, ish, 0, 0);
-  const int nb = a.nb, hi = a.hi;
-  const bool nar_b = sizeof(T) == 4 ? true : a.nar_b, nar_p = sizeof(T) == 4 ? true : a.nar_p, has_sib = a.has_sib;
-  const unsigned step_b = kLanes * (nar_b ? 8 : 16), step_p = kLanes * (nar_p ? 8 : 16);
-  const char* src_b = a.src_b;
-  const char* src_p = a.src_p;
-  auto request = [&](int b, int slot) {
-    if (b < nb) {
-      const uint32_t dst = ring_s + (uint32_t)slot * (2 * kLanes * 16);
-      if (nar_b) cp_async8(dst, src_b + (size_t)b * step_b); else cp_async16(dst, src_b + (size_t)b * step_b);
-      if (has_sib) {
-        if (nar_p) cp_async8(dst + kLanes * 16, src_p + (size_t)b * step_p); else cp_async16(dst + kLanes * 16, src_p + (size_t)b * step_p);
-      }
-    }
-    cp_async_commit();   // a group per bin, empty past the end, so the wait below always counts the same
-  };
-#pragma unroll
-  for (int d = 0; d < kScanAhead; ++d) request(d, d);
-  int slot = 0, slot_in = kScanAhead;
-  for (int b = 0; b < nb; ++b) {
-    cp_async_wait<kScanAhead - 1>();
-    T bx, by, px = 0, py = 0;
-    ring_cell(ring[slot * (2 * kLanes)], nar_b, bx, by);
-    if (has_sib) ring_cell(ring[slot * (2 * kLanes) + kLanes], nar_p, px, py);
-    request(b + kScanAhead, slot_in);
-    slot = slot + 1 == kScanRing ? 0 : slot + 1;
-    slot_in = slot_in + 1 == kScanRing ? 0 : slot_in + 1;
-    const T sx = px - bx, sy = py - by;
-    if (a.write_sib) store_cell(a.hsib, a.nar_s, a.goff + (size_t)b * kLanes, make_longlong2((long long)sx, (long long)sy));
-    const bool occupied = has_sib ? ((px | py | bx | by) != 0) : ((bx | by) != 0);
-    if (__any_sync(0xffffffffu, occupied)) {
-      const bool in_range = b < hi;
-      child_step<T, MDS>(cb, k, bx, by, b, in_range, isg, ish);
-      if (has_sib) child_step<T, MDS>(cs, k, sx, sy, b, in_range, isg, ish);
-    }
-  }
-  acc_result(cb, rb);
-  acc_result(cs, rs);
-}
-
 // One CTA = one pair, one warp per feature group: the only barriers are between the warps of that pair, and the
 // hardware CTA scheduler balances pairs of different cost (narrow / wide cells, single children, empty bins).
 __global__ void __launch_bounds__(kDeepWarps * 32, GT_DEEP_CTAS) k_scan_deep(Wave w, int level) {
   extern __shared__ uint4 s_ring[];                       // [warp][slot][built | parent][lane]
-  __shared__ float s_est[kDeepWarps][4];
   __shared__ Cand s_c[kDeepWarps][2];
   const int n_pairs = (int)w.counters[5 + (level & 1)];
   if (n_pairs < kDeepPairs || (int)blockIdx.x >= n_pairs) return;
   const int G = w.groups;                                  // == warps of this CTA (G <= 8 by kMaskWords)
   const int grp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  uint4* ring = s_ring + (size_t)grp * (kScanRing * 2 * kLanes) + lane;
+  uint4* ring = s_ring + (size_t)grp * (kRingWarpBytes / 16) + lane;
   const uint32_t ring_s = (uint32_t)__cvta_generic_to_shared(ring);
   const PairRec pr = w.pairs[blockIdx.x];
   const int j = pr.job;
@@ -988,10 +1080,10 @@ __global__ void __launch_bounds__(kDeepWarps * 32, GT_DEEP_CTAS) k_scan_deep(Wav
   const long long hmin_q = (long long)ceil((double)jp.mcw * (double)js.sh);
   LaneRes rb, rs;
   {
-    DeepArgs a;
+    WalkArgs a;
     a.has_sib = has_sib;
-    a.nb = w.grp_maxnc[jp.fold * G + grp];
-    a.hi = hi;
+    a.b0 = 0; a.b1 = w.grp_maxnc[jp.fold * G + grp]; a.hi = hi;
+    a.GLb0 = a.HLb0 = a.GLs0 = a.HLs0 = 0;
     a.write_sib = has_sib && (level + 1 < jp.max_depth);
     a.goff = goff;
     a.nar_b = nar_b; a.nar_p = nar_p;
@@ -1003,27 +1095,14 @@ __global__ void __launch_bounds__(kDeepWarps * 32, GT_DEEP_CTAS) k_scan_deep(Wav
     ChildTot tb{nodes[bnode].G, nodes[bnode].H, nodes[bnode].root_gain};
     const ChildTot ts{nodes[snode].G, nodes[snode].H, nodes[snode].root_gain};
     if (level == 0) tb.root_gain = calc_gain(jp, (double)tb.Gt * js.inv_sg, (double)tb.Ht * js.inv_sh);
-    const GainK k{jp.alpha, jp.lambda, jp.mds};
-    const bool all32 = nar_b && (!has_sib || nar_p);
-    if (k.mds == 0.0f) {
-      if (all32) deep_stage1<int, false>(k, tb, ts, hmin_q, isg, ish, a, ring, ring_s, rb, rs);
-      else deep_stage1<long long, false>(k, tb, ts, hmin_q, isg, ish, a, ring, ring_s, rb, rs);
-    } else {
-      if (all32) deep_stage1<int, true>(k, tb, ts, hmin_q, isg, ish, a, ring, ring_s, rb, rs);
-      else deep_stage1<long long, true>(k, tb, ts, hmin_q, isg, ish, a, ring, ring_s, rb, rs);
-    }
+    walk_dispatch(GainK{jp.alpha, jp.lambda, jp.mds}, tb, ts, hmin_q, isg, ish, a, ring, ring_s, rb, rs);
   }
-  float v0 = rb.e1, v1 = rb.smax, v2 = rs.e1, v3 = rs.smax;
+  float v0 = rb.e1, v2 = rs.e1;
   for (int d = 16; d; d >>= 1) {
-    v0 = fmaxf(v0, __shfl_xor_sync(0xffffffffu, v0, d)); v1 = fmaxf(v1, __shfl_xor_sync(0xffffffffu, v1, d));
-    v2 = fmaxf(v2, __shfl_xor_sync(0xffffffffu, v2, d)); v3 = fmaxf(v3, __shfl_xor_sync(0xffffffffu, v3, d));
+    v0 = fmaxf(v0, __shfl_xor_sync(0xffffffffu, v0, d)); v2 = fmaxf(v2, __shfl_xor_sync(0xffffffffu, v2, d));
   }
-  if (lane == 0) { s_est[grp][0] = v0; s_est[grp][1] = v1; s_est[grp][2] = v2; s_est[grp][3] = v3; }
-  __syncthreads();
-  v0 = v2 = -3.0e38f; v1 = v3 = 0.f;
-  for (int k = 0; k < G; ++k) {
-    v0 = fmaxf(v0, s_est[k][0]); v1 = fmaxf(v1, s_est[k][1]); v2 = fmaxf(v2, s_est[k][2]); v3 = fmaxf(v3, s_est[k][3]);
-  }
+  // stage 2 prunes with this warp's own best estimate: a weaker bound than the pair-wide one (a few more exact
+  // evaluations), but the warps of the pair meet only once, at the end
   // stage 2 and the node updates re-read the per-pair values they need: only the lane results live across the bin loop
   const double inv_sg = js.inv_sg, inv_sh = js.inv_sh;
   const float isg = (float)inv_sg, ish = (float)inv_sh;
@@ -1034,7 +1113,7 @@ __global__ void __launch_bounds__(kDeepWarps * 32, GT_DEEP_CTAS) k_scan_deep(Wav
       const int node = side == 0 ? bnode : snode;
       ChildTot t{nodes[node].G, nodes[node].H, nodes[node].root_gain};
       if (level == 0) t.root_gain = calc_gain(jp, (double)t.Gt * inv_sg, (double)t.Ht * inv_sh);
-      Cand best = lane_exact(jp, t, side == 0 ? rb : rs, side, side == 0 ? v0 : v2, side == 0 ? v1 : v3, f, 0, hi, 0, 0,
+      Cand best = lane_exact<true>(jp, t, side == 0 ? rb : rs, side, side == 0 ? v0 : v2, f, 0, hi, 0, 0,
                              hbuilt, nar_b, hpar, nar_p, goff, hmin_q, isg, ish, inv_sg, inv_sh);
       warp_merge<16>(best);
       bestc[side] = best;
@@ -1351,12 +1430,20 @@ __global__ void k_dump_node_rows(Wave w, gt_node_rows* out) {
 
 int hist_smem_bytes() { return kHistSmem; }
 
+#ifdef GT_SCAN_STATS
+extern "C" void dump_scan_stats() {
+  unsigned long long h[4];
+  cudaMemcpyFromSymbol(h, g_scan_stats, sizeof(h));
+  fprintf(stderr, "scan stats: stage-2 warp calls %llu, alive lanes %llu, column walks %llu\n", h[0], h[1], h[2]);
+}
+#endif
+
 int configure_kernels() {
   cudaError_t e = cudaFuncSetAttribute(k_hist<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmem);
   if (e != cudaSuccess) return (int)e;
   e = cudaFuncSetAttribute(k_hist<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * kHistSmem);
   if (e != cudaSuccess) return (int)e;
-  return (int)cudaFuncSetAttribute(k_scan_deep, cudaFuncAttributeMaxDynamicSharedMemorySize, kDeepWarps * kDeepWarpSmem);
+  return (int)cudaFuncSetAttribute(k_scan_deep, cudaFuncAttributeMaxDynamicSharedMemorySize, kDeepWarps * kRingWarpBytes);
 }
 
 void launch_init_wave(const Wave& w, cudaStream_t s) {
@@ -1378,7 +1465,7 @@ void launch_scan(const Wave& w, int level, cudaStream_t s) {
   const long long bound = (long long)w.lvl_jobs[level] * (level == 0 ? 1 : (1 << (level - 1)));
   const int grid = (int)(bound < 148 * 4 ? bound : 148 * 4);   // CTAs loop over the wave-wide pair list
   k_scan<<<grid, w.groups * scan_chunks(w.groups) * 32, 0, s>>>(w, level);
-  if (bound >= kDeepPairs) k_scan_deep<<<(unsigned)bound, w.groups * 32, w.groups * kDeepWarpSmem, s>>>(w, level);
+  if (bound >= kDeepPairs) k_scan_deep<<<(unsigned)bound, w.groups * 32, w.groups * kRingWarpBytes, s>>>(w, level);
 }
 void launch_plan_part(const Wave& w, int level, cudaStream_t s) { k_plan_part<<<w.lvl_jobs[level + 1], 256, 0, s>>>(w, level); }
 void launch_part_count(const Wave& w, int level, cudaStream_t s) {

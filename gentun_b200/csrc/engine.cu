@@ -644,7 +644,13 @@ int gt_engine_eval_ex(gt_engine* e, int32_t n_ind, const double* genes, const gt
   return eval_impl(e, n_ind, genes, opts, fitness_out, rounds_out, dump);
 }
 
+#ifdef GT_SCAN_STATS
+extern "C" void dump_scan_stats();
+#endif
 void gt_engine_destroy(gt_engine* e) {
+#ifdef GT_SCAN_STATS
+  dump_scan_stats();
+#endif
   if (!e) return;
   cudaSetDevice(e->device);
   if (e->stream) { cudaStreamSynchronize(e->stream); }

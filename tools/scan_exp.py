@@ -14,3 +14,4 @@ for s in range(2):
     fit, _ = eng.evaluate([genes[i] for i in shard], nfold=5, num_boost_round=rounds)
     st = eng.stats()
     print(os.path.basename(os.environ.get('GENTUN_B200_LIB', 'default')), 'eval %.1f ms  hist %.1f ms  fit0 %.9f' % (st['eval_ms'], st['hist_ms'], fit[0]), flush=True)
+eng.close()
