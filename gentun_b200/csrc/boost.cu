@@ -1456,16 +1456,19 @@ void launch_grad(const Wave& w, cudaStream_t s) {
 // Per-level launches cover only the jobs whose trees reach that level (a prefix of the depth-ordered job array).
 void launch_plan_hist(const Wave& w, int level, cudaStream_t s) { k_plan_hist<<<w.lvl_jobs[level], 256, 0, s>>>(w, level); }
 void launch_hist_zero(const Wave& w, int level, cudaStream_t s) { k_hist_zero<<<dim3(32, w.lvl_jobs[level]), 256, 0, s>>>(w, level); }
-void launch_hist(const Wave& w, int level, cudaStream_t s) {
+int launch_hist(const Wave& w, int level, cudaStream_t s) {   // returns the number of kernels launched
   int cap = hist_items_bound(w, level);
   if (w.groups % 2 == 0) k_hist<4><<<dim3(cap * (w.groups / 2), w.lvl_jobs[level]), 512, 2 * kHistSmem, s>>>(w, level);
   else k_hist<2><<<dim3(cap * w.groups, w.lvl_jobs[level]), 256, kHistSmem, s>>>(w, level);
+  return 1;
 }
-void launch_scan(const Wave& w, int level, cudaStream_t s) {
+int launch_scan(const Wave& w, int level, cudaStream_t s) {   // returns the number of kernels launched
   const long long bound = (long long)w.lvl_jobs[level] * (level == 0 ? 1 : (1 << (level - 1)));
   const int grid = (int)(bound < 148 * 4 ? bound : 148 * 4);   // CTAs loop over the wave-wide pair list
   k_scan<<<grid, w.groups * scan_chunks(w.groups) * 32, 0, s>>>(w, level);
-  if (bound >= kDeepPairs) k_scan_deep<<<(unsigned)bound, w.groups * 32, w.groups * kRingWarpBytes, s>>>(w, level);
+  if (bound < kDeepPairs) return 1;
+  k_scan_deep<<<(unsigned)bound, w.groups * 32, w.groups * kRingWarpBytes, s>>>(w, level);
+  return 2;
 }
 void launch_plan_part(const Wave& w, int level, cudaStream_t s) { k_plan_part<<<w.lvl_jobs[level + 1], 256, 0, s>>>(w, level); }
 void launch_part_count(const Wave& w, int level, cudaStream_t s) {

@@ -502,10 +502,10 @@ int eval_impl(gt_engine* e, int n_ind, const double* genes, const gt_fit_opts* o
         gt::launch_plan_hist(w, d, e->stream);
         gt::launch_hist_zero(w, d, e->stream);
         if (e->collect_timing) cudaEventRecord(get_event(ev_used++), e->stream);
-        gt::launch_hist(w, d, e->stream);
+        launches += gt::launch_hist(w, d, e->stream);
         if (e->collect_timing) cudaEventRecord(get_event(ev_used++), e->stream);
-        gt::launch_scan(w, d, e->stream);
-        launches += 4; ++hist_launches;
+        launches += gt::launch_scan(w, d, e->stream);
+        launches += 2; ++hist_launches;
         if (d + 1 < Dmax) {
           gt::launch_plan_part(w, d, e->stream);
           gt::launch_part_count(w, d, e->stream);

@@ -33,8 +33,8 @@ void launch_init_wave(const Wave& w, cudaStream_t s);
 void launch_grad(const Wave& w, cudaStream_t s);
 void launch_plan_hist(const Wave& w, int level, cudaStream_t s);
 void launch_hist_zero(const Wave& w, int level, cudaStream_t s);
-void launch_hist(const Wave& w, int level, cudaStream_t s);
-void launch_scan(const Wave& w, int level, cudaStream_t s);
+int launch_hist(const Wave& w, int level, cudaStream_t s);    // these two return how many kernels they launched
+int launch_scan(const Wave& w, int level, cudaStream_t s);
 void launch_plan_part(const Wave& w, int level, cudaStream_t s);
 void launch_part_count(const Wave& w, int level, cudaStream_t s);
 void launch_part_scatter(const Wave& w, int level, cudaStream_t s);
