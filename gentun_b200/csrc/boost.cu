@@ -1033,7 +1033,7 @@ __device__ __forceinline__ void scan_pair(const Wave& w, int level, const PairRe
 // kDeepPairs pairs use k_scan_deep (one warp per pair and feature group).  Both are launched every level
 // and decide from the device-side pair count.
 #ifndef GT_DEEP_PAIRS
-#define GT_DEEP_PAIRS 3072
+#define GT_DEEP_PAIRS 2048
 #endif
 constexpr int kDeepPairs = GT_DEEP_PAIRS;
 
@@ -1285,9 +1285,225 @@ __global__ void __launch_bounds__(256) k_part_scatter(Wave w, int level) {
 // Every row (train slice and test slice) walks the new tree on its bin bytes (bin <= split bin  <=>
 // raw value < threshold); the prediction is updated in place, test rows add their
 // metric term, train rows record the gradient range of the next round.
-__global__ void __launch_bounds__(256) k_predict(Wave w) {
-  // grid.x = job, grid.y = row chunk: CTAs that are scheduled together work on the same rows of different jobs,
-  // and the jobs of one fold share the fold's bin matrix and labels, so those lines are served from L2
+//
+// One CTA = (fold, chunk of kPredRows matrix rows).  All jobs of a fold read the same bin matrix, so the CTA stages
+// the chunk's bin rows in shared memory ONCE and then takes the fold's jobs one after the other: tree into shared
+// memory (double-buffered, the next job's nodes are fetched into registers while this job's rows are walked), each
+// thread walks its rows out of shared memory.  With one CTA per (job, chunk) reading bytes from global memory the
+// kernel was bound by L1 wavefronts (ncu: L1 99 % busy), so the shared layouts are chosen for one wavefront per access:
+//  - bin rows transposed, word (4 features) major: s_rows[word][row] -- the 32 consecutive rows of a warp hit 32
+//    different banks whatever feature each lane asks for;
+//  - tree nodes split into a 4-byte split word (feature, bin, state) and a separate leaf value, heap order: the
+//    nodes of a level are contiguous, so levels 0-5 are conflict-free and only the deep levels see random conflicts.
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+constexpr int kPredThreads = 1024;
+static_assert(sizeof(TreeNode) == 8 && kNodeCap % kPredThreads == 0, "k_predict splits TreeNode into two 32-bit words");
+constexpr int kPredRowBytes = 128 * 1024;   // staged bin rows: kPredRows x 64 bytes fit
+__host__ __device__ inline int pred_sub_rows(int fpad) {   // rows staged at a time (a chunk takes kPredRows / this many rounds)
+  int r = kPredRows;
+  while (r > 256 && (long long)r * fpad > kPredRowBytes) r >>= 1;
+  return r;
+}
+constexpr int kPredTreeBytes = 2 * kNodeCap * 8;   // two buffers of (split word, leaf value) x kNodeCap
+__host__ __device__ inline int pred_smem_bytes(int fpad, int n_inds) { return pred_sub_rows(fpad) * fpad + kPredTreeBytes + n_inds * 12; }
+
+__global__ void __launch_bounds__(kPredThreads, 1) k_predict(Wave w) {
+  extern __shared__ uint32_t s_pred[];
+  __shared__ double s_m[2][32];
+  __shared__ float s_g[2][32], s_h[2][32];
+  __shared__ int s_nact;
+  const int fold = blockIdx.x, chunk = blockIdx.y;
+  const FoldDev fd = w.folds[fold];
+  const int fpad = w.fpad, upr = fpad >> 4;   // 16-byte units per bin row
+  const int SR = pred_sub_rows(fpad);
+  uint32_t* s_split = s_pred;                                              // [2][kNodeCap] walk words, see store_tree
+  float* s_leaf = reinterpret_cast<float*>(s_pred + 2 * kNodeCap);         // [2][kNodeCap]
+  uint32_t* s_rows = s_pred + 4 * kNodeCap;                                // [fpad / 4][SR]
+  int* s_list = reinterpret_cast<int*>(s_rows + (size_t)(fpad >> 2) * SR); // active individuals of this wave, in order
+  float* s_spw = reinterpret_cast<float*>(s_list + w.n_inds);              // their scale_pos_weight ...
+  int* s_nodes = reinterpret_cast<int*>(s_spw + w.n_inds);                 // ... and node counts, by list position
+  const uint32_t split_base = (uint32_t)__cvta_generic_to_shared(s_split);
+  const uint32_t rows_base = (uint32_t)__cvta_generic_to_shared(s_rows) + threadIdx.x * 4u;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const long long c0 = (long long)chunk * kPredRows;
+  const long long chunk_rows = min((long long)kPredRows, w.n - c0);
+  constexpr int kNodesPerThread = kNodeCap / kPredThreads;
+  constexpr int R = kPredRows / kPredThreads;   // rows per thread and job, walked together so their latencies overlap
+
+  // everything the job loop needs about the jobs comes from shared memory: the CTA is alone on its SM and moves in
+  // lock step, so a global-memory round trip inside the loop would be paid in full every time
+  if (wid == 0) {
+    int cnt = 0;
+    for (int base = 0; base < w.n_inds; base += 32) {
+      const int q = base + lane;
+      const bool act = q < w.n_inds && w.js[q * w.nfold + fold].active;
+      const unsigned m = __ballot_sync(0xffffffffu, act);
+      if (act) {
+        const int pos = cnt + __popc(m & ((1u << lane) - 1u));
+        const JobParams& jp = w.jp[q * w.nfold + fold];
+        s_list[pos] = q; s_spw[pos] = jp.spw; s_nodes[pos] = (2 << jp.max_depth) - 1;
+      }
+      cnt += __popc(m);
+    }
+    if (lane == 0) s_nact = cnt;
+  }
+  __syncthreads();
+  const int n_act = s_nact;
+
+  // job at list position `k` of the previous loop step left its per-warp partial results in s_*[par]: fold and publish
+  auto publish = [&](int k, int par, bool first_sub) {
+    if (wid != 0) return;
+    float gm = s_g[par][lane], hm = s_h[par][lane];
+    double ms = s_m[par][lane];
+    for (int d = 16; d; d >>= 1) {
+      gm = fmaxf(gm, __shfl_xor_sync(0xffffffffu, gm, d));
+      hm = fmaxf(hm, __shfl_xor_sync(0xffffffffu, hm, d));
+      ms += __shfl_xor_sync(0xffffffffu, ms, d);
+    }
+    if (lane == 0) {
+      const int j = s_list[k] * w.nfold + fold;
+      if (gm > 0.f) atomicMax(&w.js[j].gmax_bits, __float_as_uint(gm));
+      if (hm > 0.f) atomicMax(&w.js[j].hmax_bits, __float_as_uint(hm));
+      double* mp = w.mpart + (size_t)j * w.pred_chunks + chunk;
+      *mp = first_sub ? ms : *mp + ms;
+    }
+  };
+  uint2 tn[kNodesPerThread];   // next job's nodes on their way from global to shared memory
+  auto fetch_tree = [&](int k) {
+    const uint2* src = reinterpret_cast<const uint2*>(w.tree + (size_t)(s_list[k] * w.nfold + fold) * kNodeCap);
+    const int n_nodes = s_nodes[k];
+#pragma unroll
+    for (int q = 0; q < kNodesPerThread; ++q) {
+      const int i = threadIdx.x + q * kPredThreads;
+      tn[q] = i < n_nodes ? src[i] : make_uint2(0u, 0u);
+    }
+  };
+  auto store_tree = [&](int buf) {
+#pragma unroll
+    for (int q = 0; q < kNodesPerThread; ++q) {
+      const int i = threadIdx.x + q * kPredThreads;
+      s_leaf[buf * kNodeCap + i] = __uint_as_float(tn[q].x);
+      // walk word: bits 24-31 split bin, bit 23 = split node, bits 2-22 byte offset of the feature's word row in
+      // s_rows, bits 0-1 the feature's byte inside that word -- each field one instruction away from its use
+      const uint32_t feat = tn[q].y & 0xffffu, sbin = (tn[q].y >> 16) & 0xffu;
+      const bool is_split = (tn[q].y >> 24) == (uint32_t)kSplit;
+      s_split[buf * kNodeCap + i] = is_split ? (sbin << 24) | 0x800000u | (((feat >> 2) * (uint32_t)SR * 4u) & 0x7ffffcu) | (feat & 3u) : 0u;
+    }
+  };
+
+  for (long long s0 = 0; s0 < chunk_rows; s0 += SR) {
+    const int sub_rows = (int)min((long long)SR, chunk_rows - s0);
+    const bool first_sub = s0 == 0;
+    __syncthreads();   // the previous sub-chunk's rows and trees are no longer read
+    for (int part = 0; part < upr; ++part)
+      for (int lr = threadIdx.x; lr < sub_rows; lr += kPredThreads) {
+        const uint4 v = *(reinterpret_cast<const uint4*>(fd.bins + (size_t)(c0 + s0 + lr) * fpad) + part);
+        uint32_t* dst = s_rows + (size_t)(part * 4) * SR + lr;
+        dst[0] = v.x; dst[SR] = v.y; dst[2 * SR] = v.z; dst[3 * SR] = v.w;
+      }
+    // per-row values that do not depend on the job
+    float yv[R];
+    bool is_train[R], have[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int i = threadIdx.x + r * kPredThreads;
+      have[r] = i < sub_rows;
+      const long long row = c0 + s0 + i;
+      yv[r] = have[r] ? fd.y[row] : 0.f;
+      is_train[r] = row < fd.ntrain;
+    }
+    const bool any_train = c0 + s0 < fd.ntrain, any_test = c0 + s0 + sub_rows > fd.ntrain;   // CTA-uniform
+    float pn[R];   // the next job's current predictions, requested a job ahead
+    auto fetch_pred = [&](int k) {
+      const float* pred = w.pred + (size_t)(s_list[k] * w.nfold + fold) * w.n + c0 + s0;
+#pragma unroll
+      for (int r = 0; r < R; ++r) pn[r] = have[r] ? pred[threadIdx.x + r * kPredThreads] : 0.f;
+    };
+    // with few (fold, chunk) pairs the job list is dealt over gridDim.z CTAs, so that a small matrix still fills the GPU
+    const int kz = blockIdx.z, Z = gridDim.z;
+    if (kz < n_act) { fetch_tree(kz); store_tree(0); fetch_pred(kz); }
+    int it = 0;
+    for (int k = kz; k < n_act; k += Z, ++it) {
+      const int par = it & 1;
+      __syncthreads();   // tree of this job is in buffer par; everyone has left the previous job; the rows are staged
+      float p0[R];
+#pragma unroll
+      for (int r = 0; r < R; ++r) p0[r] = pn[r];
+      if (k + Z < n_act) { fetch_tree(k + Z); fetch_pred(k + Z); }
+      if (it > 0) publish(k - Z, par ^ 1, first_sub);
+      const float spw = s_spw[k];
+      const float* leaf = s_leaf + par * kNodeCap;
+      int nid[R];
+      uint32_t t[R];
+      bool go = false;
+      const uint32_t split_s = split_base + (uint32_t)par * (kNodeCap * 4u);
+#pragma unroll
+      for (int r = 0; r < R; ++r) { nid[r] = 0; t[r] = lds_u32(split_s); go |= (t[r] & 0x800000u) != 0u; }
+      while (go) {
+        go = false;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          if (t[r] & 0x800000u) {
+            const uint32_t word = lds_u32(rows_base + (t[r] & 0x7ffffcu) + (uint32_t)r * (kPredThreads * 4u));
+            const uint32_t bin = __byte_perm(word, 0u, 0x4440u | (t[r] & 3u));
+            nid[r] = 2 * nid[r] + 1 + (bin > __byte_perm(t[r], 0u, 0x4443u) ? 1 : 0);
+            t[r] = lds_u32(split_s + (uint32_t)nid[r] * 4u);
+            go |= (t[r] & 0x800000u) != 0u;
+          }
+        }
+      }
+      float* pred = w.pred + (size_t)(s_list[k] * w.nfold + fold) * w.n + c0 + s0;
+      float gm = 0.f, hm = 0.f;
+      double msum = 0.0;
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        if (!have[r]) continue;
+        const float p = p0[r] + leaf[nid[r]];
+        pred[threadIdx.x + r * kPredThreads] = p;
+        const float y = yv[r];
+        if (is_train[r]) {
+          float g, h;
+          grad_pair(w.objective, p, y, spw, g, h);
+          gm = fmaxf(gm, fabsf(g)); hm = fmaxf(hm, fabsf(h));
+        } else {
+          const float pv = w.objective == 1 ? sigmoid_x(p) : p;
+          float e;
+          if (w.metric == 1) {     // EvalRowLogLoss
+            const float eps = 1e-16f, pneg = 1.0f - pv;
+            if (pv < eps) e = -y * logf(eps) - (1.0f - y) * logf(1.0f - eps);
+            else if (pneg < eps) e = -y * logf(1.0f - eps) - (1.0f - y) * logf(eps);
+            else e = -y * logf(pv) - (1.0f - y) * logf(pneg);
+          } else {                 // EvalRowRMSE
+            const float d = y - pv;
+            e = d * d;
+          }
+          msum += (double)e;
+        }
+      }
+      if (k + Z < n_act) store_tree(par ^ 1);
+      // a chunk lies in the train slice, in the test slice, or (one chunk per fold) across the boundary: only the
+      // reductions it needs.  |g|, |h| >= 0, so their float order is the order of their bit patterns.
+      if (any_train) {
+        gm = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(gm)));
+        hm = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(hm)));
+      }
+      if (any_test)
+        for (int d = 16; d; d >>= 1) msum += __shfl_xor_sync(0xffffffffu, msum, d);
+      if (lane == 0) { s_g[par][wid] = gm; s_h[par][wid] = hm; s_m[par][wid] = msum; }
+    }
+    __syncthreads();
+    if (it > 0) publish(kz + (it - 1) * Z, (it - 1) & 1, first_sub);
+  }
+}
+
+// Small-matrix variant: one CTA per (job, chunk), bytes read straight from global memory.  With only a handful of
+// (fold, chunk) pairs -- winequality has 9 -- the kernel above cannot fill the GPU without re-staging the rows for every
+// few jobs, and its start-up (job list, staging, first tree) is then most of its run time.
+__global__ void __launch_bounds__(256) k_predict_small(Wave w) {
   const int j = blockIdx.x;
   const int chunk = blockIdx.y;
   const JobState& js = w.js[j];
@@ -1443,6 +1659,8 @@ int configure_kernels() {
   if (e != cudaSuccess) return (int)e;
   e = cudaFuncSetAttribute(k_hist<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * kHistSmem);
   if (e != cudaSuccess) return (int)e;
+  e = cudaFuncSetAttribute(k_predict, cudaFuncAttributeMaxDynamicSharedMemorySize, kPredRowBytes + kPredTreeBytes + kMaxWaveInds * 12);
+  if (e != cudaSuccess) return (int)e;
   return (int)cudaFuncSetAttribute(k_scan_deep, cudaFuncAttributeMaxDynamicSharedMemorySize, kDeepWarps * kRingWarpBytes);
 }
 
@@ -1477,7 +1695,16 @@ void launch_part_count(const Wave& w, int level, cudaStream_t s) {
 void launch_part_scatter(const Wave& w, int level, cudaStream_t s) {
   k_part_scatter<<<dim3(part_items_bound(w, level), w.lvl_jobs[level + 1]), 256, 0, s>>>(w, level);
 }
-void launch_predict(const Wave& w, cudaStream_t s) { k_predict<<<dim3(w.n_jobs, w.pred_chunks), 256, 0, s>>>(w); }
+void launch_predict(const Wave& w, cudaStream_t s) {
+  const int ctas = w.nfold * w.pred_chunks;
+  if (ctas < 148) {   // fewer (fold, chunk) pairs than SMs
+    k_predict_small<<<dim3(w.n_jobs, w.pred_chunks), 256, 0, s>>>(w);
+    return;
+  }
+  int z = (2 * 148 + ctas - 1) / ctas;   // two CTAs' worth of work items per SM, if the wave has that many jobs
+  z = z < 1 ? 1 : z > w.n_inds ? w.n_inds : z;
+  k_predict<<<dim3(w.nfold, w.pred_chunks, z), kPredThreads, pred_smem_bytes(w.fpad, w.n_inds), s>>>(w);
+}
 void launch_round_end(const Wave& w, int first, double* fitness_out, int* rounds_out, cudaStream_t s) {
   k_round_end<<<w.n_inds, 32, 0, s>>>(w, first, fitness_out, rounds_out);
 }

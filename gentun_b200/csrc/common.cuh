@@ -17,6 +17,7 @@ constexpr int kQuantBits = 19;      // |quantised gradient|, quantised hessian <
 constexpr int kQuantBitsH = 17;     // hessians are near-constant (1 for squared error): fewer bits, fewer flushes
 constexpr int kPredRows = 2048;     // rows per predict CTA
 constexpr int kMaskWords = 8;       // feature masks: up to 256 features
+constexpr int kMaxWaveInds = 4096;  // individuals per wave (k_predict keeps their job list in shared memory)
 
 enum NodeState : uint8_t { kAbsent = 0, kOpen = 1, kSplit = 2, kLeaf = 3 };
 

@@ -373,7 +373,7 @@ int eval_impl(gt_engine* e, int n_ind, const double* genes, const gt_fit_opts* o
     int b = 0;
     while (b < n_ind) {
       size_t used = 0; int q = b;
-      while (q < n_ind && (q - b + 1) * nfold <= 16384) {
+      while (q < n_ind && (q - b + 1) * nfold <= 16384 && (q - b + 1) <= gt::kMaxWaveInds) {
         size_t need = job_bytes((int)genes[(size_t)order[q] * GT_NUM_GENES + 2]) * (size_t)nfold;
         if (used + need > budget) break;
         used += need; ++q;

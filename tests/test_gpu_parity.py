@@ -272,6 +272,32 @@ def test_wide_feature_matrices_parity(f):
     ctx.close()
 
 
+@pytest.mark.parametrize("f,classification", [(20, False), (100, True), (200, False)])
+def test_fold_shared_prediction_kernel_parity(f, classification):
+    """At least 148 (fold, chunk) pairs switch the prediction update to the kernel that stages a chunk's bin rows in
+    shared memory once for all jobs of the fold: 64-, 128- and 256-byte rows (one, two and four staging rounds per
+    chunk), both metrics, the chunk that straddles the train/test boundary, and an individual that stops early
+    while the others go on."""
+    from gentun_b200.engine import Engine
+    x, y = make_dataset(80000, f, seed=3000 + f, classification=classification)
+    eng = Engine(x, y)
+    ctx = orc.Context(x, y, 5)
+    gs = [genes(max_depth=8, eta=0.3, min_child_weight=0), genes(max_depth=3, eta=1.0, **{'lambda': 0.0}),
+          genes(max_depth=5, eta=0.1, subsample=0.7, scale_pos_weight=1.7 if classification else 1.0)]
+    params = dict(nfold=5, num_boost_round=14, early_stopping_rounds=2)
+    if classification:
+        params.update(objective="binary:logistic", eval_metric="logloss")
+    fit, rounds = eng.evaluate(gs, **params)
+    fit2, rounds2 = eng.evaluate(gs[::-1], **params)
+    assert np.array_equal(fit, fit2[::-1]) and np.array_equal(rounds, rounds2[::-1])
+    for i, g in enumerate(gs):
+        want = ctx.cv(g, orc.make_opts(**params))
+        assert rounds[i] == want["rounds"], (f, i, rounds[i], want["rounds"])
+        assert rel(fit[i], want["fitness"]) < REL_TOL, (f, i, fit[i], want["fitness"])
+    eng.close()
+    ctx.close()
+
+
 def test_logistic_logloss_parity():
     from gentun_b200.engine import Engine
     x, y = make_dataset(30000, 12, seed=1004, classification=True)
