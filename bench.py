@@ -217,12 +217,30 @@ def run_reference(args):
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line))
+    emit(line)
     return 0
+
+
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """stdout must carry the one JSON line and nothing else, but libraries write there too (NCCL prints its version
+    banner to stdout when the box sets NCCL_DEBUG): point fd 1 at stderr for the run and keep the real stdout aside."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    sys.stdout.flush()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, (json.dumps(line) + "\n").encode())
 
 
 def main():
     args = parse_args()
+    quiet_stdout()
     if args.rounds:
         wl = list(WORKLOADS[args.workload]); wl[3] = args.rounds
         WORKLOADS[args.workload + "-profile"] = tuple(wl)
@@ -242,7 +260,6 @@ def main():
     torch.cuda.set_device(local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # stdout carries the JSON line and nothing else
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     def barrier():
@@ -363,7 +380,7 @@ def main():
                 "sample": "oracle port (no xgboost on this box): individual 0 of the seeded population, full per-fit "
                           "set-up (folds + sketch + binning, %.1f s) + %d of %d rounds x %d folds (%.1f s), extrapolated "
                           "linearly to %d rounds" % (detail["setup_s"], args.cpu_rounds, rounds, nfold, detail["rounds_s"], rounds)}
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
