@@ -20,11 +20,14 @@ def _dist():
 
 def fit_cost(genes):
     """Relative device time of one individual's CV fit.  Measured on a B200 with tools/cost_model.py (random
-    batches of the seeded 1M x 50 population, least squares, 3 % rms error): the time is set by the tree
-    depth -- a term per level and a term per node of the deepest levels -- and hardly at all by the sampling
-    genes, because the levels with many small nodes are bound by the split scan, not by the rows."""
+    batches of the seeded 1M x 50 population at 100 rounds, least squares, 4 % rms error per batch of 16): the
+    time is set by the tree depth -- a term per level and a term per node of the deepest levels -- hardly at all
+    by the sampling genes (the levels with many small nodes are bound by the split scan, not by the rows), and
+    it falls with the learning rate: a large eta shrinks the residuals quickly, later trees find fewer valid
+    splits and stay smaller."""
     d = float(genes["max_depth"])
-    return 1.7 + 2.8 * d + 21.8 * 2.0 ** (d - 10.0)
+    e = min(float(genes.get("eta", 0.3)), 0.2)
+    return 11.5 + 8.1 * d + 61.1 * 2.0 ** (d - 10.0) - e * (159.5 * 2.0 ** (d - 10.0) + 10.5 * d)
 
 
 def shard_plan(costs, world_size):
