@@ -803,9 +803,12 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
+// A cell out of the ring.  32-bit walks (T = int) take the low words of an int64 cell: they are used only when both
+// children's sums fit 32 bits, and then parent - built is right modulo 2^32 whatever the parent's own magnitude.
 template <typename T>
 __device__ __forceinline__ void ring_cell(const uint4 v, bool narrow, T& x, T& y) {
-  if (sizeof(T) == 4 || narrow) { x = (T)(int)v.x; y = (T)(int)v.y; return; }
+  if (narrow) { x = (T)(int)v.x; y = (T)(int)v.y; return; }
+  if (sizeof(T) == 4) { x = (T)(int)v.x; y = (T)(int)v.z; return; }
   x = (T)(long long)(((unsigned long long)v.y << 32) | v.x);
   y = (T)(long long)(((unsigned long long)v.w << 32) | v.z);
 }
@@ -826,7 +829,7 @@ __device__ __forceinline__ void walk_stage1(const GainK k, const ChildTot& tb, c
   acc_init(cb, tb, k, hmin_q, isg, ish, a.GLb0, a.HLb0);
   acc_init(cs, ts, k, hmin_q, isg, ish, a.GLs0, a.HLs0);
   const int b0 = a.b0, b1 = a.b1, hi = a.hi;
-  const bool nar_b = sizeof(T) == 4 ? true : a.nar_b, nar_p = sizeof(T) == 4 ? true : a.nar_p, has_sib = a.has_sib;
+  const bool nar_b = sizeof(T) == 4 ? true : a.nar_b, nar_p = a.nar_p, has_sib = a.has_sib;
   const unsigned step_b = kLanes * (nar_b ? 8 : 16), step_p = kLanes * (nar_p ? 8 : 16);
   const char* src_b = a.src_b;
   const char* src_p = a.src_p;
@@ -867,7 +870,7 @@ __device__ __forceinline__ void walk_stage1(const GainK k, const ChildTot& tb, c
 
 __device__ __forceinline__ void walk_dispatch(const GainK k, const ChildTot& tb, const ChildTot& ts, long long hmin_q, float isg, float ish,
                                               const WalkArgs& a, uint4* ring, uint32_t ring_s, LaneRes& rb, LaneRes& rs) {
-  const bool all32 = a.nar_b && (!a.has_sib || a.nar_p);   // every prefix of the pair fits 32 bits
+  const bool all32 = a.nar_b && (!a.has_sib || a.nar_s);   // both children's sums fit 32 bits (the parent's need not)
   if (k.mds == 0.0f) {
     if (all32) walk_stage1<int, false>(k, tb, ts, hmin_q, isg, ish, a, ring, ring_s, rb, rs);
     else walk_stage1<long long, false>(k, tb, ts, hmin_q, isg, ish, a, ring, ring_s, rb, rs);
@@ -987,7 +990,7 @@ __device__ __forceinline__ void scan_pair(const Wave& w, int level, const PairRe
   LaneRes rb, rs;
   {
     const GainK k{jp.alpha, jp.lambda, jp.mds};
-    const bool all32 = nar_b && (!has_sib || nar_p);   // every prefix of the pair fits 32 bits
+    const bool all32 = nar_b && (!has_sib || nar_s);   // both children's sums fit 32 bits (the parent's need not)
     if (k.mds == 0.0f) {
       if (all32) chunk_stage1<int, false>(k, tb, ts, hmin_q, isg, ish, GLb0, HLb0, GLs0, HLs0, hbuilt, nar_b, hpar, nar_p, has_sib, goff, b_lo, hi, rb, rs);
       else chunk_stage1<long long, false>(k, tb, ts, hmin_q, isg, ish, GLb0, HLb0, GLs0, HLs0, hbuilt, nar_b, hpar, nar_p, has_sib, goff, b_lo, hi, rb, rs);
@@ -1194,13 +1197,18 @@ __global__ void __launch_bounds__(256) k_part_count(Wave w, int level) {
   const uint8_t* col = w.folds[jp.fold].bins_col + (size_t)nd.feat * (size_t)w.n;
   const uint32_t* src = w.ridx + ((size_t)j * 2 + it.buf) * w.nt_stride + it.begin;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  uint32_t* flags = w.pflags + ((size_t)j * w.part_cap + blockIdx.x) * (kPartRows / 32);
   int cnt = 0;
 #pragma unroll
   for (int t = 0; t < kPartRows / 256; ++t) {
     const uint32_t p = (uint32_t)t * 256u + threadIdx.x;
     bool left = false;
     if (p < it.cnt) left = (uint32_t)col[src[p]] <= sbin;
-    cnt += __popc(__ballot_sync(0xffffffffu, left));
+    const uint32_t word = __ballot_sync(0xffffffffu, left);
+    // the scatter pass takes the decision from here instead of gathering the bin byte again (a 32-byte sector per row
+    // once the node's rows are sparse)
+    if (lane == 0) flags[t * 8 + wid] = word;
+    cnt += __popc(word);
   }
   __shared__ int s_cnt[8];
   if (lane == 0) s_cnt[wid] = cnt;
@@ -1216,11 +1224,8 @@ __global__ void __launch_bounds__(256) k_part_scatter(Wave w, int level) {
   const int j = blockIdx.y;
   const JobState& js = w.js[j];
   if ((int)blockIdx.x >= js.n_part_items) return;
-  const JobParams& jp = w.jp[j];
   const PartItem it = w.pitems[(size_t)j * w.part_cap + blockIdx.x];
-  const Node& nd = w.nodes[(size_t)j * kNodeCap + it.node];
-  const uint32_t sbin = nd.bin;
-  const uint8_t* col = w.folds[jp.fold].bins_col + (size_t)nd.feat * (size_t)w.n;
+  const uint32_t* flags = w.pflags + ((size_t)j * w.part_cap + blockIdx.x) * (kPartRows / 32);
   const int* pleft = w.pleft + (size_t)j * w.part_cap;
   const uint32_t* src = w.ridx + ((size_t)j * 2 + it.buf) * w.nt_stride + it.begin;
   uint32_t* dst = w.ridx + ((size_t)j * 2 + (it.buf ^ 1)) * w.nt_stride;
@@ -1242,10 +1247,8 @@ __global__ void __launch_bounds__(256) k_part_scatter(Wave w, int level) {
 #pragma unroll
   for (int t = 0; t < kIters; ++t) {
     const uint32_t p = (uint32_t)t * 256u + threadIdx.x;
-    bool left = false;
-    rows[t] = 0u;
-    if (p < it.cnt) { rows[t] = src[p]; left = (uint32_t)col[rows[t]] <= sbin; }
-    words[t] = __ballot_sync(0xffffffffu, left);
+    rows[t] = p < it.cnt ? src[p] : 0u;
+    words[t] = flags[t * 8 + wid];   // written by k_part_count
     if (lane == 0) s_pref[t * 8 + wid] = __popc(words[t]);
   }
   __syncthreads();

@@ -124,7 +124,7 @@ struct EvalBuffers {
   DevBuf<gt::JobParams> d_jp; DevBuf<gt::JobState> d_js; DevBuf<gt::IndState> d_is;
   DevBuf<gt::Node> d_nodes; DevBuf<gt::TreeNode> d_tree; DevBuf<float> d_pred; DevBuf<int2> d_gq;
   DevBuf<uint32_t> d_ridx; DevBuf<gt::HistEntry> d_hist; DevBuf<gt::HistItem> d_hitems; DevBuf<int> d_zlist;
-  DevBuf<gt::PairRec> d_pairs; DevBuf<gt::PartItem> d_pitems; DevBuf<int> d_pleft;
+  DevBuf<gt::PairRec> d_pairs; DevBuf<gt::PartItem> d_pitems; DevBuf<int> d_pleft; DevBuf<uint32_t> d_pflags;
   DevBuf<double> d_mpart; DevBuf<double> d_trace; DevBuf<unsigned long long> d_counters;
   DevBuf<double> d_fit; DevBuf<int> d_rounds; DevBuf<gt_tree_node> d_trees; DevBuf<gt_node_rows> d_nrows;
 };
@@ -359,7 +359,7 @@ int eval_impl(gt_engine* e, int n_ind, const double* genes, const gt_fit_opts* o
     b += hist_cells_for_depth(D, e->groups) * sizeof(gt::HistEntry);
     b += (size_t)gt::kNodeCap * (sizeof(gt::Node) + sizeof(gt::TreeNode));
     b += (size_t)hist_cap * (sizeof(gt::HistItem) + 4) + (size_t)pair_cap * sizeof(gt::PairRec);
-    b += (size_t)part_cap * (sizeof(gt::PartItem) + 4) + (size_t)pred_chunks * 8;
+    b += (size_t)part_cap * (sizeof(gt::PartItem) + 4 + gt::kPartRows / 8) + (size_t)pred_chunks * 8;
     b += sizeof(gt::JobParams) + sizeof(gt::JobState);
     return b;
   };
@@ -393,7 +393,7 @@ int eval_impl(gt_engine* e, int n_ind, const double* genes, const gt_fit_opts* o
   EvalBuffers& B = e->bufs;
   auto &d_jp = B.d_jp; auto &d_js = B.d_js; auto &d_is = B.d_is; auto &d_nodes = B.d_nodes; auto &d_tree = B.d_tree;
   auto &d_pred = B.d_pred; auto &d_gq = B.d_gq; auto &d_ridx = B.d_ridx; auto &d_hist = B.d_hist; auto &d_hitems = B.d_hitems;
-  auto &d_zlist = B.d_zlist; auto &d_pairs = B.d_pairs; auto &d_pitems = B.d_pitems; auto &d_pleft = B.d_pleft;
+  auto &d_zlist = B.d_zlist; auto &d_pairs = B.d_pairs; auto &d_pitems = B.d_pitems; auto &d_pleft = B.d_pleft; auto &d_pflags = B.d_pflags;
   auto &d_mpart = B.d_mpart; auto &d_trace = B.d_trace; auto &d_counters = B.d_counters; auto &d_fit = B.d_fit;
   auto &d_rounds = B.d_rounds; auto &d_trees = B.d_trees; auto &d_nrows = B.d_nrows;
   GT_CUDA(d_jp.ensure(max_jobs)); GT_CUDA(d_js.ensure(max_jobs)); GT_CUDA(d_is.ensure(max_inds));
@@ -402,7 +402,7 @@ int eval_impl(gt_engine* e, int n_ind, const double* genes, const gt_fit_opts* o
   GT_CUDA(d_ridx.ensure(max_jobs * 2 * (size_t)nt_stride)); GT_CUDA(d_hist.ensure(max_hist));
   GT_CUDA(d_hitems.ensure(max_jobs * hist_cap)); GT_CUDA(d_zlist.ensure(max_jobs * hist_cap));
   GT_CUDA(d_pairs.ensure(max_jobs * pair_cap)); GT_CUDA(d_pitems.ensure(max_jobs * part_cap));
-  GT_CUDA(d_pleft.ensure(max_jobs * part_cap));
+  GT_CUDA(d_pleft.ensure(max_jobs * part_cap)); GT_CUDA(d_pflags.ensure(max_jobs * part_cap * (gt::kPartRows / 32)));
   GT_CUDA(d_mpart.ensure(max_jobs * pred_chunks)); GT_CUDA(d_counters.ensure(8));
   GT_CUDA(d_fit.ensure(n_ind)); GT_CUDA(d_rounds.ensure(n_ind));
   const bool want_trace = dump && dump->trace_means;
@@ -489,7 +489,7 @@ int eval_impl(gt_engine* e, int n_ind, const double* genes, const gt_fit_opts* o
     w.folds = fs->d_folds.p; w.grp_maxnc = fs->d_grp_maxnc.p;
     w.jp = d_jp.p; w.js = d_js.p; w.is = d_is.p; w.nodes = d_nodes.p; w.tree = d_tree.p; w.pred = d_pred.p;
     w.gq = d_gq.p; w.ridx = d_ridx.p; w.hist = d_hist.p; w.hitems = d_hitems.p; w.zlist = d_zlist.p;
-    w.pairs = d_pairs.p; w.pitems = d_pitems.p; w.pleft = d_pleft.p; w.mpart = d_mpart.p;
+    w.pairs = d_pairs.p; w.pitems = d_pitems.p; w.pleft = d_pleft.p; w.pflags = d_pflags.p; w.mpart = d_mpart.p;
     w.trace = want_trace ? d_trace.p : nullptr; w.counters = d_counters.p;
 
     gt::launch_init_wave(w, e->stream); ++launches;
