@@ -624,6 +624,20 @@ int gt_engine_create(const float* X, int64_t n, int32_t f, int64_t ldx, const fl
     memcpy(e->h_y.data(), y, sizeof(float) * n);
     e->d_X = e->own_X.p; e->d_y = e->own_y.p;
   }
+  {
+    DevBuf<unsigned long long> d_bad;
+    unsigned long long h_bad[2] = {0, 0};
+    GT_CUDA(d_bad.ensure(2));
+    GT_CUDA(cudaMemsetAsync(d_bad.p, 0, sizeof(h_bad), e->stream));
+    gt::launch_count_nonfinite(e->d_X, n, f, ldx, e->d_y, d_bad.p, e->stream);
+    GT_CUDA(cudaMemcpyAsync(h_bad, d_bad.p, sizeof(h_bad), cudaMemcpyDeviceToHost, e->stream));
+    GT_CUDA(cudaStreamSynchronize(e->stream));
+    if (h_bad[0] || h_bad[1]) {
+      cudaStreamDestroy(e->stream);
+      return fail(GT_ERR_ARG, "%llu values of X and %llu labels are NaN or inf: xgb.DMatrix would treat NaN as missing and refuse inf; "
+                  "this engine has no missing-value path", h_bad[0], h_bad[1]);
+    }
+  }
   *out = e.release();
   return GT_OK;
 }

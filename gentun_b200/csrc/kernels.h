@@ -24,6 +24,7 @@ void launch_bin(const float* X, long long ldx, int f, int fpad, const uint32_t* 
                 const float* cuts, const int* ncuts, uint8_t* bins, cudaStream_t s);
 void launch_bins_to_columns(const uint8_t* bins, int f, int fpad, long long n, uint8_t* out, cudaStream_t s);
 void launch_gather_y(const float* y, const uint32_t* rows, long long n, float* out, cudaStream_t s);
+void launch_count_nonfinite(const float* X, long long n, int f, long long ldx, const float* y, unsigned long long* out /* [2], zeroed */, cudaStream_t s);
 
 // engine.cu: message returned by gt_last_error() for the calling thread
 void set_error_message(const char* msg);

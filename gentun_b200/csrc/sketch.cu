@@ -629,6 +629,28 @@ void launch_bins_to_columns(const uint8_t* bins, int f, int fpad, long long n, u
   k_bins_to_columns<<<148 * 16, 256, 0, s>>>(bins, f, fpad, n, out);
 }
 
+// xgb.DMatrix treats NaN as "missing" and refuses inf; this engine has no missing-value path, so both are counted
+// here and refused at gt_engine_create instead of flowing into the sketch as ordinary numbers.
+static __global__ void k_count_nonfinite(const float* X, long long n, int f, long long ldx, const float* y, unsigned long long* out) {
+  unsigned long long bad_x = 0, bad_y = 0;
+  const long long total = n * f;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / f;
+    const int c = (int)(i - r * f);
+    if (!isfinite(X[r * ldx + c])) ++bad_x;
+  }
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    if (!isfinite(y[i])) ++bad_y;
+  bad_x = __reduce_add_sync(0xffffffffu, (unsigned)bad_x);
+  bad_y = __reduce_add_sync(0xffffffffu, (unsigned)bad_y);
+  if ((threadIdx.x & 31) == 0) {
+    if (bad_x) atomicAdd(&out[0], bad_x);
+    if (bad_y) atomicAdd(&out[1], bad_y);
+  }
+}
+void launch_count_nonfinite(const float* X, long long n, int f, long long ldx, const float* y, unsigned long long* out, cudaStream_t s) {
+  k_count_nonfinite<<<148 * 8, 256, 0, s>>>(X, n, f, ldx, y, out);
+}
 void launch_gather_y(const float* y, const uint32_t* rows, long long n, float* out, cudaStream_t s) {
   int blocks = (int)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
   if (blocks < 1) blocks = 1;

@@ -343,6 +343,23 @@ def test_bad_genes_are_rejected(wine_pair):
         eng.evaluate([genes()], nfold=1, num_boost_round=2)
 
 
+def test_missing_values_and_inf_are_refused():
+    """xgb.DMatrix treats NaN as missing and refuses inf; the engine has no missing-value path and must say so
+    instead of binning NaN as a number."""
+    from gentun_b200.engine import Engine
+    x, y = make_dataset(3000, 6, seed=5)
+    bad = x.copy(); bad[17, 3] = np.nan
+    with pytest.raises(ValueError, match="NaN"):
+        Engine(bad, y)
+    bad = x.copy(); bad[0, 0] = np.inf
+    with pytest.raises(ValueError):
+        Engine(bad, y)
+    ybad = y.copy(); ybad[5] = np.nan
+    with pytest.raises(ValueError):
+        Engine(x, ybad)
+    Engine(x, y).close()
+
+
 # ---------------------------------------------------------------- the drop-in API on the GPU
 def test_xgboost_model_and_population_drop_in(wine):
     """The reference's tests/test_xgboost_model.py and tests/test_wine-quality.py flows (shortened)."""
