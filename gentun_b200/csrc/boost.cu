@@ -1186,6 +1186,13 @@ __global__ void __launch_bounds__(256) k_plan_part(Wave w, int level) {
 
 // The split feature's bin of a row comes from the feature-major copy of the bin matrix: rows of a node
 // are ascending, so neighbouring rows share DRAM lines (1 useful byte per 64-byte line otherwise).
+// Two passes over a node's rows in items of kPartRows rows.  Pass 1 gathers the split feature's bin byte of every row,
+// keeps the goes-left decision as one bit per row and counts the lefts of the item; pass 2 turns the bits into
+// stable destinations (item-local ranks from the bits alone, item offsets from the counts of the node's earlier
+// items) and moves the row ids.  Items are large so that a CTA lives long enough to amortise its start.
+constexpr int kPartWords = kPartRows / 32;   // goes-left words per item
+static_assert(kPartWords % 8 == 0, "one word per warp and iteration");
+
 __global__ void __launch_bounds__(256) k_part_count(Wave w, int level) {
   const int j = blockIdx.y;
   const JobState& js = w.js[j];
@@ -1197,18 +1204,27 @@ __global__ void __launch_bounds__(256) k_part_count(Wave w, int level) {
   const uint8_t* col = w.folds[jp.fold].bins_col + (size_t)nd.feat * (size_t)w.n;
   const uint32_t* src = w.ridx + ((size_t)j * 2 + it.buf) * w.nt_stride + it.begin;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  uint32_t* flags = w.pflags + ((size_t)j * w.part_cap + blockIdx.x) * (kPartRows / 32);
+  uint32_t* flags = w.pflags + ((size_t)j * w.part_cap + blockIdx.x) * kPartWords;
   int cnt = 0;
+  const int iters = (int)((it.cnt + 255u) / 256u);   // CTA-uniform
+  for (int t0 = 0; t0 < iters; t0 += 8) {
+    uint32_t rows[8];
+    uint32_t bins[8];
 #pragma unroll
-  for (int t = 0; t < kPartRows / 256; ++t) {
-    const uint32_t p = (uint32_t)t * 256u + threadIdx.x;
-    bool left = false;
-    if (p < it.cnt) left = (uint32_t)col[src[p]] <= sbin;
-    const uint32_t word = __ballot_sync(0xffffffffu, left);
-    // the scatter pass takes the decision from here instead of gathering the bin byte again (a 32-byte sector per row
-    // once the node's rows are sparse)
-    if (lane == 0) flags[t * 8 + wid] = word;
-    cnt += __popc(word);
+    for (int q = 0; q < 8; ++q) {
+      const uint32_t p = (uint32_t)(t0 + q) * 256u + threadIdx.x;
+      rows[q] = p < it.cnt ? src[p] : 0xffffffffu;
+    }
+#pragma unroll
+    for (int q = 0; q < 8; ++q) bins[q] = rows[q] != 0xffffffffu ? (uint32_t)col[rows[q]] : 0xffffffffu;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      const uint32_t word = __ballot_sync(0xffffffffu, bins[q] <= sbin);   // rows past the end compare as 2^32 - 1: right
+      if (t0 + q < iters) {
+        if (lane == 0) flags[(t0 + q) * 8 + wid] = word;
+        cnt += __popc(word);
+      }
+    }
   }
   __shared__ int s_cnt[8];
   if (lane == 0) s_cnt[wid] = cnt;
@@ -1225,15 +1241,16 @@ __global__ void __launch_bounds__(256) k_part_scatter(Wave w, int level) {
   const JobState& js = w.js[j];
   if ((int)blockIdx.x >= js.n_part_items) return;
   const PartItem it = w.pitems[(size_t)j * w.part_cap + blockIdx.x];
-  const uint32_t* flags = w.pflags + ((size_t)j * w.part_cap + blockIdx.x) * (kPartRows / 32);
+  const uint32_t* flags = w.pflags + ((size_t)j * w.part_cap + blockIdx.x) * kPartWords;
   const int* pleft = w.pleft + (size_t)j * w.part_cap;
   const uint32_t* src = w.ridx + ((size_t)j * 2 + it.buf) * w.nt_stride + it.begin;
   uint32_t* dst = w.ridx + ((size_t)j * 2 + (it.buf ^ 1)) * w.nt_stride;
-  constexpr int kIters = kPartRows / 256;
-  __shared__ int s_pref[kIters * 8];
+  __shared__ int s_pref[kPartWords];   // lefts of the item in front of each 32-row word
+  __shared__ int s_warp[8];
   __shared__ int s_red[2][8];
-  __shared__ int s_prev, s_total;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int words = (int)((it.cnt + 31u) / 32u);
+  // lefts of the node's earlier items, and of the whole node
   int prevL = 0, totL = 0;
   for (int i = it.first_item + threadIdx.x; i < it.first_item + it.n_items; i += blockDim.x) {
     const int v = pleft[i];
@@ -1242,37 +1259,59 @@ __global__ void __launch_bounds__(256) k_part_scatter(Wave w, int level) {
   }
   for (int d = 16; d; d >>= 1) { prevL += __shfl_xor_sync(0xffffffffu, prevL, d); totL += __shfl_xor_sync(0xffffffffu, totL, d); }
   if (lane == 0) { s_red[0][wid] = prevL; s_red[1][wid] = totL; }
-  uint32_t rows[kIters];
-  uint32_t words[kIters];
+  // exclusive scan of the words' left counts (word index = iteration * 8 + warp, i.e. row order); a thread takes
+  // kWordsPerThread consecutive words
+  {
+    constexpr int kWordsPerThread = (kPartWords + 255) / 256;
+    int c[kWordsPerThread], mine = 0;
 #pragma unroll
-  for (int t = 0; t < kIters; ++t) {
-    const uint32_t p = (uint32_t)t * 256u + threadIdx.x;
-    rows[t] = p < it.cnt ? src[p] : 0u;
-    words[t] = flags[t * 8 + wid];   // written by k_part_count
-    if (lane == 0) s_pref[t * 8 + wid] = __popc(words[t]);
+    for (int q = 0; q < kWordsPerThread; ++q) {
+      const int i = (int)threadIdx.x * kWordsPerThread + q;
+      c[q] = i < words ? __popc(flags[i]) : 0;
+      mine += c[q];
+    }
+    int incl = mine;
+    for (int d = 1; d < 32; d <<= 1) { const int o = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += o; }
+    if (lane == 31) s_warp[wid] = incl;
+    __syncthreads();
+    int run = incl - mine;
+    for (int q = 0; q < wid; ++q) run += s_warp[q];
+#pragma unroll
+    for (int q = 0; q < kWordsPerThread; ++q) {
+      const int i = (int)threadIdx.x * kWordsPerThread + q;
+      if (i < kPartWords) s_pref[i] = run;
+      run += c[q];
+    }
   }
   __syncthreads();
-  if (threadIdx.x == 0) {
-    int a = 0, b = 0;
-    for (int q2 = 0; q2 < 8; ++q2) { a += s_red[0][q2]; b += s_red[1][q2]; }
-    s_prev = a; s_total = b;
-    int run = 0;
-    for (int q2 = 0; q2 < kIters * 8; ++q2) { const int c = s_pref[q2]; s_pref[q2] = run; run += c; }
-  }
-  __syncthreads();
-  prevL = s_prev; totL = s_total;
+  prevL = 0; totL = 0;
+  for (int q = 0; q < 8; ++q) { prevL += s_red[0][q]; totL += s_red[1][q]; }
   const uint32_t rel0 = it.begin - it.node_begin;
+  const int iters = (int)((it.cnt + 255u) / 256u);
+  // eight iterations at a time: all their loads first (the stores below go to the other half of the same array, so
+  // the compiler would not move a load above an earlier store by itself)
+  for (int t0 = 0; t0 < iters; t0 += 8) {
+    uint32_t rows[8], wordv[8];
+    int pref[8];
 #pragma unroll
-  for (int t = 0; t < kIters; ++t) {
-    const uint32_t p = (uint32_t)t * 256u + threadIdx.x;
-    if (p < it.cnt) {
-      const uint32_t word = words[t];
-      const int lrank = s_pref[t * 8 + wid] + __popc(word & ((1u << lane) - 1u));
-      const bool left = (word >> lane) & 1u;
-      const uint32_t rel = rel0 + p;
-      const uint32_t d = left ? it.node_begin + (uint32_t)(prevL + lrank)
-                              : it.node_begin + (uint32_t)totL + (rel - (uint32_t)(prevL + lrank));
-      dst[d] = rows[t];
+    for (int q = 0; q < 8; ++q) {
+      const int t = t0 + q;
+      const uint32_t p = (uint32_t)t * 256u + threadIdx.x;
+      rows[q] = p < it.cnt ? src[p] : 0u;
+      wordv[q] = t < iters ? flags[t * 8 + wid] : 0u;
+      pref[q] = t < iters ? s_pref[t * 8 + wid] : 0;
+    }
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      const uint32_t p = (uint32_t)(t0 + q) * 256u + threadIdx.x;
+      if (p < it.cnt) {
+        const int lrank = pref[q] + __popc(wordv[q] & ((1u << lane) - 1u));
+        const bool left = (wordv[q] >> lane) & 1u;
+        const uint32_t rel = rel0 + p;
+        const uint32_t d = left ? it.node_begin + (uint32_t)(prevL + lrank)
+                                : it.node_begin + (uint32_t)totL + (rel - (uint32_t)(prevL + lrank));
+        dst[d] = rows[q];
+      }
     }
   }
   if ((int)blockIdx.x == it.first_item && threadIdx.x == 0) {

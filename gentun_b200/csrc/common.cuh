@@ -12,7 +12,10 @@ constexpr int kNodeCap = 2048;      // heap slots per tree (2^(10+1)-1 used)
 constexpr int kHistRows = 16384;    // rows per histogram work item
 constexpr int kEpochRows = 2048;    // rows between int32-overflow checks of the shared partial sums
 constexpr int kNarrowRows = 4095;   // nodes up to this many rows keep int32 histogram cells: 4095 * 2^19 < 2^31
-constexpr int kPartRows = 2048;     // rows per partition work item
+#ifndef GT_PART_ROWS
+#define GT_PART_ROWS 8192
+#endif
+constexpr int kPartRows = GT_PART_ROWS;   // rows per partition work item
 constexpr int kQuantBits = 19;      // |quantised gradient|, quantised hessian <= 2^19 (one epoch adds < 2^30)
 constexpr int kQuantBitsH = 17;     // hessians are near-constant (1 for squared error): fewer bits, fewer flushes
 constexpr int kPredRows = 2048;     // rows per predict CTA
