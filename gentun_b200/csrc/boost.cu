@@ -86,6 +86,7 @@ __device__ void prepare_next_round(const Wave& w, int j) {
   Node& r = w.nodes[(size_t)j * kNodeCap];
   r.G = 0; r.H = 0; r.begin = 0; r.cnt = (uint32_t)w.folds[jp.fold].ntrain;
   r.leaf = 0.f; r.root_gain = 0.f; r.loss_chg = 0.f; r.feat = -1; r.bin = 0; r.state = kOpen; r.buf = 0;
+  r.narrow = r.cnt <= (uint32_t)kNarrowRows; r.absG = 0ull;
   TreeNode& t = w.tree[(size_t)j * kNodeCap];
   t.leaf = 0.f; t.feat = -1; t.bin = 0; t.state = kOpen;
 }
@@ -297,9 +298,14 @@ __device__ __forceinline__ HistEntry* node_hist(const Wave& w, const JobParams& 
   return w.hist + ((level & 1) ? jp.hist_off[1] : jp.hist_off[0]) + (size_t)(node - level_first(level)) * w.groups * (kBins * kLanes);
 }
 
-// A node with at most kNarrowRows rows keeps its histogram as int32 pairs (|cell| <= rows * 2^19 < 2^31):
-// half the bytes for the deep levels, where histogram traffic dominates.  Larger nodes use int64 pairs.
-__device__ __forceinline__ bool node_narrow(uint32_t cnt) { return cnt <= (uint32_t)kNarrowRows; }
+// A node keeps its histogram as int32 pairs ("narrow": half the bytes, and a 32-bit split scan) when no cell can
+// exceed 31 bits.  |cell| <= sum of |g_q| over the node's rows <= the same sum over its parent's rows, which is known
+// exactly when the node gets its rows (Node::absG: k_hist for the root and every built child, parent - built for a
+// sibling); without that, rows * 2^19 bounds it.  Only nodes built by one CTA qualify (plain stores).  Else int64 pairs.
+__device__ __forceinline__ bool child_narrow(const Node& parent, uint32_t cnt, long long H) {
+  if (cnt <= (uint32_t)kNarrowRows) return true;
+  return cnt <= (uint32_t)kHistRows && parent.absG <= 0x7fffffffull && H <= 0x7fffffffll;
+}
 __device__ __forceinline__ longlong2 load_cell(const HistEntry* slot, bool narrow, size_t idx) {
   if (narrow) { const int2 v = reinterpret_cast<const int2*>(slot)[idx]; return make_longlong2((long long)v.x, (long long)v.y); }
   return reinterpret_cast<const longlong2*>(slot)[idx];
@@ -465,14 +471,15 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 3 : 1) k_
     asm volatile("mov.u32 %0, %1;" : "=r"(cs[s]) : "r"(v));   // opaque: keep it in a register, never rematerialise
   }
   const bool shared_node = it.flags & 1;
-  const bool never_early = !shared_node && cnt <= (uint32_t)kNarrowRows;   // owned narrow node: the whole node fits int32
+  Node& node = w.nodes[(size_t)j * kNodeCap + it.node];
+  const bool never_early = !shared_node && node.narrow;   // owned narrow node: no cell of it can leave 31 bits
   bool stored = false;                                                     // owned wide node: has an early flush happened
   // three-deep software pipeline: row ids two iterations ahead, bin bytes + gradients one ahead
   HistStage<UNITS> cur, nxt;
   hist_load<UNITS>(cur, row_b, rslot, bins_unit, gq, fpad);
   row_b = row_c;
   const uint32_t n_iter = (cnt + kStride - 1) / kStride;   // CTA-uniform trip count
-  unsigned acc_g = 0u, acc_h = 0u;
+  unsigned acc_g = 0u, acc_h = 0u, abs_rows = 0u;   // abs_rows: this lane's share of the node's sum of |g_q| (< 2^27 per item)
   for (uint32_t itn = 0; itn < n_iter; ++itn) {
     const uint32_t p2 = my0 + (itn + 2) * kStride;
     row_c = p2 < cnt ? ridx[p2] : 0xffffffffu;
@@ -488,6 +495,7 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 3 : 1) k_
       // epoch boundary: will another epoch of worst-case rows still fit in int32?
       const unsigned tg = __reduce_add_sync(0xffffffffu, acc_g >> 3), th = __reduce_add_sync(0xffffffffu, acc_h >> 3);
       if (lane == 0) { atomicAdd(&s_abs[0], (tg >> 3) + 5u); atomicAdd(&s_abs[1], (th >> 3) + 5u); }   // +5: rounding slack
+      abs_rows += acc_g;
       acc_g = 0u; acc_h = 0u;
       __syncthreads();
       // s_abs is an upper bound, in units of 64, of sum |g_q| (sum h_q) accumulated since the last flush
@@ -501,6 +509,11 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 3 : 1) k_
         __syncthreads();
       }
     }
+  }
+  // the node's exact sum of |g_q| decides the cell format of its children (child_narrow)
+  if (cg == 0) {
+    const unsigned warp_abs = __reduce_add_sync(0xffffffffu, abs_rows + acc_g);
+    if (lane == 0 && warp_abs) atomicAdd(&node.absG, (unsigned long long)warp_abs);
   }
   __syncthreads();
   hist_flush<UNITS>(w, jp, level, it, cg, sh,
@@ -772,7 +785,7 @@ __device__ __forceinline__ void settle_node(const JobParams& jp, int level, Node
   chn.leaf = jp.eta * calc_weight(jp, g, h);
   chn.root_gain = calc_gain(jp, g, h);
   chn.loss_chg = 0.f; chn.feat = -1; chn.bin = 0; chn.state = child_state;
-  chn.begin = 0; chn.cnt = 0; chn.buf = 0;
+  chn.begin = 0; chn.cnt = 0; chn.buf = 0; chn.narrow = 0; chn.absG = 0ull;
   tree[2 * node + 1 + sd] = TreeNode{chn.leaf, (int16_t)-1, (uint8_t)0, child_state};
 }
 
@@ -949,8 +962,8 @@ __device__ __forceinline__ void scan_pair(const Wave& w, int level, const PairRe
   const HistEntry* hbuilt = node_hist(w, jp, level, bnode);
   const HistEntry* hpar = has_sib ? node_hist(w, jp, level - 1, pr.parent) : nullptr;
   HistEntry* hsib = node_hist(w, jp, level, snode);
-  const bool nar_b = node_narrow(nodes[bnode].cnt), nar_s = node_narrow(nodes[snode].cnt);
-  const bool nar_p = has_sib ? node_narrow(nodes[pr.parent].cnt) : false;
+  const bool nar_b = nodes[bnode].narrow, nar_s = nodes[snode].narrow;
+  const bool nar_p = has_sib ? (bool)nodes[pr.parent].narrow : false;
   const double inv_sg = js.inv_sg, inv_sh = js.inv_sh;
   const float isg = (float)inv_sg, ish = (float)inv_sh;
   const int b_lo = ch * CB, b_hi = min(b_lo + CB, maxnc);
@@ -1029,6 +1042,7 @@ __device__ __forceinline__ void scan_pair(const Wave& w, int level, const PairRe
   best.b = __shfl_sync(0xffffffffu, best.b, 0);
   best.GL = __shfl_sync(0xffffffffu, best.GL, 0); best.HL = __shfl_sync(0xffffffffu, best.HL, 0);
   if (lane > 1) return;
+  if (side == 1 && lane == 0) nodes[snode].absG = nodes[pr.parent].absG - nodes[bnode].absG;   // exact: both are sums over rows
   settle_node(jp, level, nodes, tree, side == 0 ? bnode : snode, side == 0 ? tb : ts, best, inv_sg, inv_sh, hmin_q, lane);
 }
 
@@ -1077,7 +1091,7 @@ __global__ void __launch_bounds__(kDeepWarps * 32, GT_DEEP_CTAS) k_scan_deep(Wav
   const bool factive = f < w.f && ((js.lmask[f >> 5] >> (f & 31)) & 1u);
   const int hi = factive ? nc : 0;
   const size_t goff = (size_t)grp * (kBins * kLanes) + lane;
-  const bool nar_b = node_narrow(nodes[bnode].cnt), nar_p = has_sib ? node_narrow(nodes[pr.parent].cnt) : false;
+  const bool nar_b = nodes[bnode].narrow, nar_p = has_sib ? (bool)nodes[pr.parent].narrow : false;
   const HistEntry* hbuilt = node_hist(w, jp, level, bnode);
   const HistEntry* hpar = has_sib ? node_hist(w, jp, level - 1, pr.parent) : nullptr;
   const long long hmin_q = (long long)ceil((double)jp.mcw * (double)js.sh);
@@ -1090,7 +1104,7 @@ __global__ void __launch_bounds__(kDeepWarps * 32, GT_DEEP_CTAS) k_scan_deep(Wav
     a.write_sib = has_sib && (level + 1 < jp.max_depth);
     a.goff = goff;
     a.nar_b = nar_b; a.nar_p = nar_p;
-    a.nar_s = node_narrow(nodes[snode].cnt);
+    a.nar_s = nodes[snode].narrow;
     a.src_b = reinterpret_cast<const char*>(hbuilt) + goff * (nar_b ? 8 : 16);
     a.src_p = has_sib ? reinterpret_cast<const char*>(hpar) + goff * (nar_p ? 8 : 16) : nullptr;
     a.hsib = node_hist(w, jp, level, snode);
@@ -1135,6 +1149,7 @@ __global__ void __launch_bounds__(kDeepWarps * 32, GT_DEEP_CTAS) k_scan_deep(Wav
     const int node = side == 0 ? bnode : snode;
     ChildTot t{nodes[node].G, nodes[node].H, nodes[node].root_gain};
     if (level == 0) t.root_gain = calc_gain(jp, (double)t.Gt * inv_sg, (double)t.Ht * inv_sh);
+    if (lane == 2) nodes[snode].absG = nodes[pr.parent].absG - nodes[bnode].absG;   // exact: both are sums over rows
     settle_node(jp, level, nodes, w.tree + (size_t)j * kNodeCap, node, t, best, inv_sg, inv_sh, hmin_q, lane & 1);
   }
 }
@@ -1320,6 +1335,8 @@ __global__ void __launch_bounds__(256) k_part_scatter(Wave w, int level) {
     Node& R = nodes[2 * it.node + 2];
     L.begin = it.node_begin; L.cnt = (uint32_t)totL; L.buf = (uint8_t)(it.buf ^ 1);
     R.begin = it.node_begin + (uint32_t)totL; R.cnt = it.node_cnt - (uint32_t)totL; R.buf = (uint8_t)(it.buf ^ 1);
+    const Node& P = nodes[it.node];
+    L.narrow = child_narrow(P, L.cnt, L.H); R.narrow = child_narrow(P, R.cnt, R.H);
   }
 }
 

@@ -11,7 +11,7 @@ constexpr int kMaxDepth = 10;       // max_depth gene range 3..10 (gentun/indivi
 constexpr int kNodeCap = 2048;      // heap slots per tree (2^(10+1)-1 used)
 constexpr int kHistRows = 16384;    // rows per histogram work item
 constexpr int kEpochRows = 2048;    // rows between int32-overflow checks of the shared partial sums
-constexpr int kNarrowRows = 4095;   // nodes up to this many rows keep int32 histogram cells: 4095 * 2^19 < 2^31
+constexpr int kNarrowRows = 4095;   // nodes up to this many rows keep int32 histogram cells whatever their gradients: 4095 * 2^19 < 2^31
 #ifndef GT_PART_ROWS
 #define GT_PART_ROWS 8192
 #endif
@@ -36,7 +36,9 @@ struct Node {          // working record of one heap slot
   uint8_t bin;
   uint8_t state;
   uint8_t buf;
-  uint8_t pad[3];
+  uint8_t narrow;      // histogram cells are int32 pairs (decided when the node gets its rows)
+  uint8_t pad[2];
+  unsigned long long absG;   // sum of |g_q| over the node's rows: bounds every cell of its histogram and of its children's
 };
 
 struct TreeNode {      // compact record read by the prediction kernel, 8 B
