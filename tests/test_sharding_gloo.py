@@ -63,6 +63,26 @@ def test_shard_plan_balances_depths():
     assert abs(sums[0] - sums[1]) <= 2
 
 
+def test_shard_plan_by_fit_cost_is_balanced_and_deterministic():
+    from gentun_b200.sharding import fit_cost, shard_plan
+    from tests.synth import seeded_population_genes
+    genes = seeded_population_genes(256)
+    costs = [fit_cost(g) for g in genes]
+    assert min(costs) > 0
+    for world in (2, 4, 8):
+        plan = shard_plan(costs, world)
+        assert sorted(np.concatenate(plan).tolist()) == list(range(256))
+        assert {len(p) for p in plan} == {256 // world}                      # equal counts
+        loads = [sum(costs[i] for i in p) for p in plan]
+        assert max(loads) / (sum(loads) / world) < 1.01                      # within 1 % under the model
+        again = shard_plan(costs, world)
+        assert all(np.array_equal(a, b) for a, b in zip(plan, again))
+    # deeper trees and smaller learning rates cost more
+    base = dict(genes[0])
+    assert fit_cost(dict(base, max_depth=10)) > fit_cost(dict(base, max_depth=4))
+    assert fit_cost(dict(base, max_depth=10, eta=0.01)) > fit_cost(dict(base, max_depth=10, eta=0.5))
+
+
 def test_single_process_path_calls_the_engine_once():
     from gentun_b200 import sharding
 
