@@ -443,7 +443,6 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 3 : 1) k_
   const JobParams& jp = w.jp[j];
   const HistItem it = w.hitems[(size_t)j * w.hist_cap + item_idx];
   extern __shared__ int sh[];   // [group in CTA][g plane | h plane][bin][feature lane]
-  __shared__ unsigned s_abs[2];  // sum |g_q| and sum h_q since the last flush, in units of 64
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   // row ids of the first two iterations are requested before the shared histogram is cleared, so that the
   // clear overlaps the first of the three dependent loads (item -> row id -> bin line)
@@ -453,7 +452,6 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 3 : 1) k_
   uint32_t row_b = my0 < cnt ? ridx[my0] : 0xffffffffu;                              // iteration 0
   uint32_t row_c = my0 + kStride < cnt ? ridx[my0 + kStride] : 0xffffffffu;          // iteration 1
   for (int i = threadIdx.x; i < kGroupsPerCta * 2 * kBins * kLanes / 4; i += kThreads) reinterpret_cast<int4*>(sh)[i] = make_int4(0, 0, 0, 0);
-  if (threadIdx.x < 2) s_abs[threadIdx.x] = 0u;
   __syncthreads();
   const int rslot = lane / UNITS, unit = lane % UNITS;
   const int rot = UNITS == 2 ? rslot : rslot * 2 + (unit >> 1);   // 16 distinct rotations per bank half
@@ -480,6 +478,7 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 3 : 1) k_
   row_b = row_c;
   const uint32_t n_iter = (cnt + kStride - 1) / kStride;   // CTA-uniform trip count
   unsigned acc_g = 0u, acc_h = 0u, abs_rows = 0u;   // abs_rows: this lane's share of the node's sum of |g_q| (< 2^27 per item)
+  unsigned run_g = 0u, run_h = 0u;                  // this warp's sums since the CTA's last flush
   for (uint32_t itn = 0; itn < n_iter; ++itn) {
     const uint32_t p2 = my0 + (itn + 2) * kStride;
     row_c = p2 < cnt ? ridx[p2] : 0xffffffffu;
@@ -492,20 +491,22 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 3 : 1) k_
     cur = nxt;
     row_b = row_c;
     if ((itn + 1) % kEpochIters == 0 && itn + 1 < n_iter) {
-      // epoch boundary: will another epoch of worst-case rows still fit in int32?
-      const unsigned tg = __reduce_add_sync(0xffffffffu, acc_g >> 3), th = __reduce_add_sync(0xffffffffu, acc_h >> 3);
-      if (lane == 0) { atomicAdd(&s_abs[0], (tg >> 3) + 5u); atomicAdd(&s_abs[1], (th >> 3) + 5u); }   // +5: rounding slack
+      // epoch boundary: will another epoch of worst-case rows still fit in int32?  Every cell is bounded by the sum,
+      // over the CTA's warps, of the |g_q| (h_q) each has accumulated since the last flush; rows are dealt to the
+      // warps round-robin, so each warp holds its own sum against an equal share of what the int32 range leaves
+      // after a worst-case epoch, and one barrier collects the verdict.
+      run_g += __reduce_add_sync(0xffffffffu, acc_g);
+      run_h += __reduce_add_sync(0xffffffffu, acc_h);
       abs_rows += acc_g;
       acc_g = 0u; acc_h = 0u;
-      __syncthreads();
-      // s_abs is an upper bound, in units of 64, of sum |g_q| (sum h_q) accumulated since the last flush
-      const unsigned lim = (0x7fffffffu >> 6) - (((unsigned)kEpochRows << kQuantBits) >> 6) - 64u;
-      const bool must = (s_abs[0] >= lim || s_abs[1] >= lim) && !never_early;
-      __syncthreads();
+      constexpr unsigned kWarps = kThreads / 32;
+      constexpr unsigned lim_g = (0x7fffffffu - ((unsigned)kEpochRows << kQuantBits)) / kWarps;
+      constexpr unsigned lim_h = (0x7fffffffu - ((unsigned)kEpochRows << kQuantBitsH)) / kWarps;
+      const bool must = __syncthreads_or((run_g >= lim_g || run_h >= lim_h) && !never_early);
       if (must) {
         hist_flush<UNITS>(w, jp, level, it, cg, sh, shared_node ? kFlushAtomic : stored ? kFlushAddWide : kFlushStoreWide, true);
         stored = true;
-        if (threadIdx.x < 2) s_abs[threadIdx.x] = 0u;
+        run_g = 0u; run_h = 0u;
         __syncthreads();
       }
     }
@@ -1359,7 +1360,10 @@ __device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
   return v;
 }
-constexpr int kPredThreads = 1024;
+#ifndef GT_PRED_THREADS
+#define GT_PRED_THREADS 1024
+#endif
+constexpr int kPredThreads = GT_PRED_THREADS;   // kPredRows / kPredThreads rows per thread and job
 static_assert(sizeof(TreeNode) == 8 && kNodeCap % kPredThreads == 0, "k_predict splits TreeNode into two 32-bit words");
 constexpr int kPredRowBytes = 128 * 1024;   // staged bin rows: kPredRows x 64 bytes fit
 __host__ __device__ inline int pred_sub_rows(int fpad) {   // rows staged at a time (a chunk takes kPredRows / this many rounds)
@@ -1416,8 +1420,9 @@ __global__ void __launch_bounds__(kPredThreads, 1) k_predict(Wave w) {
   // job at list position `k` of the previous loop step left its per-warp partial results in s_*[par]: fold and publish
   auto publish = [&](int k, int par, bool first_sub) {
     if (wid != 0) return;
-    float gm = s_g[par][lane], hm = s_h[par][lane];
-    double ms = s_m[par][lane];
+    constexpr int kWarps = kPredThreads / 32;
+    float gm = lane < kWarps ? s_g[par][lane] : 0.f, hm = lane < kWarps ? s_h[par][lane] : 0.f;
+    double ms = lane < kWarps ? s_m[par][lane] : 0.0;
     for (int d = 16; d; d >>= 1) {
       gm = fmaxf(gm, __shfl_xor_sync(0xffffffffu, gm, d));
       hm = fmaxf(hm, __shfl_xor_sync(0xffffffffu, hm, d));
