@@ -23,6 +23,10 @@ namespace {
 
 constexpr float kRtEps = 1e-6f;
 constexpr int kHistSmem = 2 * kBins * kLanes * (int)sizeof(int);   // g plane + h plane = 64 KiB
+#ifndef GT_HIST_SMEM_PAD
+#define GT_HIST_SMEM_PAD 0
+#endif
+constexpr int kHistPad = GT_HIST_SMEM_PAD;   // experiment: unused shared memory, i.e. a smaller L1
 
 // ------------------------------------------------------------------ split arithmetic
 __device__ __forceinline__ double thr_l1(double w, float alpha) {
@@ -459,6 +463,12 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 3 : 1) k_
   const int rb = (rot & 3) * 8;
   const uint8_t* bins_unit = w.folds[jp.fold].bins + (size_t)cg * kGroupsPerCta * kLanes + unit * 16;
   const int2* gq = w.gq + (size_t)j * w.nt_stride;
+#ifdef GT_HIST_OPAQUE
+  // opaque copies: under register pressure the compiler otherwise re-derives both base pointers from the kernel
+  // parameters (constant loads and 64-bit multiplies) for every load of the main loop
+  asm volatile("mov.u64 %0, %0;" : "+l"(bins_unit));
+  asm volatile("mov.u64 %0, %0;" : "+l"(gq));
+#endif
   const int fpad = w.fpad;
   const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(sh);
   uint32_t cs[16];   // shared address of this lane's feature column (bin 0, g plane) at unrolled step s
@@ -1721,7 +1731,7 @@ extern "C" void dump_scan_stats() {
 int configure_kernels() {
   cudaError_t e = cudaFuncSetAttribute(k_hist<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmem);
   if (e != cudaSuccess) return (int)e;
-  e = cudaFuncSetAttribute(k_hist<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * kHistSmem);
+  e = cudaFuncSetAttribute(k_hist<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * kHistSmem + kHistPad);
   if (e != cudaSuccess) return (int)e;
   e = cudaFuncSetAttribute(k_predict, cudaFuncAttributeMaxDynamicSharedMemorySize, kPredRowBytes + kPredTreeBytes + kMaxWaveInds * 12);
   if (e != cudaSuccess) return (int)e;
@@ -1740,7 +1750,7 @@ void launch_plan_hist(const Wave& w, int level, cudaStream_t s) { k_plan_hist<<<
 void launch_hist_zero(const Wave& w, int level, cudaStream_t s) { k_hist_zero<<<dim3(32, w.lvl_jobs[level]), 256, 0, s>>>(w, level); }
 int launch_hist(const Wave& w, int level, cudaStream_t s) {   // returns the number of kernels launched
   int cap = hist_items_bound(w, level);
-  if (w.groups % 2 == 0) k_hist<4><<<dim3(cap * (w.groups / 2), w.lvl_jobs[level]), 512, 2 * kHistSmem, s>>>(w, level);
+  if (w.groups % 2 == 0) k_hist<4><<<dim3(cap * (w.groups / 2), w.lvl_jobs[level]), 512, 2 * kHistSmem + kHistPad, s>>>(w, level);
   else k_hist<2><<<dim3(cap * w.groups, w.lvl_jobs[level]), 256, kHistSmem, s>>>(w, level);
   return 1;
 }
