@@ -23,10 +23,6 @@ namespace {
 
 constexpr float kRtEps = 1e-6f;
 constexpr int kHistSmem = 2 * kBins * kLanes * (int)sizeof(int);   // g plane + h plane = 64 KiB
-#ifndef GT_HIST_SMEM_PAD
-#define GT_HIST_SMEM_PAD 0
-#endif
-constexpr int kHistPad = GT_HIST_SMEM_PAD;   // experiment: unused shared memory, i.e. a smaller L1
 
 // ------------------------------------------------------------------ split arithmetic
 __device__ __forceinline__ double thr_l1(double w, float alpha) {
@@ -434,7 +430,7 @@ __device__ __forceinline__ void hist_flush(const Wave& w, const JobParams& jp, i
 }
 
 template <int UNITS>
-__global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 3 : 1) k_hist(Wave w, int level) {
+__global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 2 : 1) k_hist(Wave w, int level) {
   constexpr int kThreads = UNITS == 2 ? 256 : 512;
   constexpr int kGroupsPerCta = UNITS / 2;
   constexpr uint32_t kStride = (kThreads / 32) * 32u;          // rows per CTA iteration
@@ -1731,7 +1727,7 @@ extern "C" void dump_scan_stats() {
 int configure_kernels() {
   cudaError_t e = cudaFuncSetAttribute(k_hist<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmem);
   if (e != cudaSuccess) return (int)e;
-  e = cudaFuncSetAttribute(k_hist<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * kHistSmem + kHistPad);
+  e = cudaFuncSetAttribute(k_hist<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * kHistSmem);
   if (e != cudaSuccess) return (int)e;
   e = cudaFuncSetAttribute(k_predict, cudaFuncAttributeMaxDynamicSharedMemorySize, kPredRowBytes + kPredTreeBytes + kMaxWaveInds * 12);
   if (e != cudaSuccess) return (int)e;
@@ -1750,7 +1746,7 @@ void launch_plan_hist(const Wave& w, int level, cudaStream_t s) { k_plan_hist<<<
 void launch_hist_zero(const Wave& w, int level, cudaStream_t s) { k_hist_zero<<<dim3(32, w.lvl_jobs[level]), 256, 0, s>>>(w, level); }
 int launch_hist(const Wave& w, int level, cudaStream_t s) {   // returns the number of kernels launched
   int cap = hist_items_bound(w, level);
-  if (w.groups % 2 == 0) k_hist<4><<<dim3(cap * (w.groups / 2), w.lvl_jobs[level]), 512, 2 * kHistSmem + kHistPad, s>>>(w, level);
+  if (w.groups % 2 == 0) k_hist<4><<<dim3(cap * (w.groups / 2), w.lvl_jobs[level]), 512, 2 * kHistSmem, s>>>(w, level);
   else k_hist<2><<<dim3(cap * w.groups, w.lvl_jobs[level]), 256, kHistSmem, s>>>(w, level);
   return 1;
 }
