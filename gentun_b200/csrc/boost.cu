@@ -459,12 +459,6 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 2 : 1) k_
   const int rb = (rot & 3) * 8;
   const uint8_t* bins_unit = w.folds[jp.fold].bins + (size_t)cg * kGroupsPerCta * kLanes + unit * 16;
   const int2* gq = w.gq + (size_t)j * w.nt_stride;
-#ifdef GT_HIST_OPAQUE
-  // opaque copies: under register pressure the compiler otherwise re-derives both base pointers from the kernel
-  // parameters (constant loads and 64-bit multiplies) for every load of the main loop
-  asm volatile("mov.u64 %0, %0;" : "+l"(bins_unit));
-  asm volatile("mov.u64 %0, %0;" : "+l"(gq));
-#endif
   const int fpad = w.fpad;
   const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(sh);
   uint32_t cs[16];   // shared address of this lane's feature column (bin 0, g plane) at unrolled step s
