@@ -341,7 +341,7 @@ __device__ __forceinline__ uint4 ld_stream(const uint4* p) {
 // UNITS = 16-byte units of a row handled by one CTA: 2 = one feature group (32 B of the row, 64 KiB of
 // shared histogram, 3 CTAs/SM), 4 = a pair of groups (the whole 64-byte line of the row, 128 KiB, 1 CTA/SM).
 template <int UNITS>
-struct HistStage { uint4 b[UNITS]; int2 g[UNITS]; };
+struct HistStage { uint4 b[UNITS]; int2 gv; };   // gv: gradient pair of THIS lane's row; sub-batches take theirs by shuffle
 
 __device__ __forceinline__ void red_shared(uint32_t addr, int v) {
   asm volatile("red.shared.add.s32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
@@ -361,8 +361,9 @@ __device__ __forceinline__ void hist_load(HistStage<UNITS>& st, uint32_t myrow, 
     const bool ok = r != 0xffffffffu;
     const uint32_t a = ok ? r : 0u;
     st.b[sb] = ld_stream(reinterpret_cast<const uint4*>(bins_unit + (size_t)a * fpad));
-    st.g[sb] = ok ? gq[a] : make_int2(0, 0);
   }
+  // one coalesced gather for the warp's 32 rows (each lane its own row) instead of one per sub-batch
+  st.gv = myrow != 0xffffffffu ? gq[myrow] : make_int2(0, 0);
 }
 
 __device__ __forceinline__ void hist_accumulate(const uint4 v, const int2 g2, bool q1, bool q2, int rb, const uint32_t (&cs)[16]) {
@@ -485,9 +486,11 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 2 : 1) k_
     if (itn + 1 < n_iter) hist_load<UNITS>(nxt, row_b, rslot, bins_unit, gq, fpad);
 #pragma unroll
     for (int sb = 0; sb < UNITS; ++sb) {
-      hist_accumulate(cur.b[sb], cur.g[sb], q1, q2, rb, cs);
-      if (unit == 0) { acc_g += (unsigned)abs(cur.g[sb].x); acc_h += (unsigned)cur.g[sb].y; }   // one lane per row
+      const int src = sb * (32 / UNITS) + rslot;
+      const int2 g2 = make_int2(__shfl_sync(0xffffffffu, cur.gv.x, src), __shfl_sync(0xffffffffu, cur.gv.y, src));
+      hist_accumulate(cur.b[sb], g2, q1, q2, rb, cs);
     }
+    acc_g += (unsigned)abs(cur.gv.x); acc_h += (unsigned)cur.gv.y;   // every lane holds one row of the iteration
     cur = nxt;
     row_b = row_c;
     if ((itn + 1) % kEpochIters == 0 && itn + 1 < n_iter) {
