@@ -470,7 +470,8 @@ typedef struct {
   int64_t* ntrain; int64_t* ntest;
   int64_t** train_rows; int64_t** test_rows;   /* original row ids, DMatrix.slice order */
   float** cuts; int32_t** ncuts; float** min_vals;
-  uint8_t** bins_col;                          /* [f][ntrain] column-major train bins */
+  uint8_t** bins_col;                          /* [f][ntrain] column-major train bins (partition) */
+  uint8_t** bins_row;                          /* [ntrain][f] row-major train bins (histograms: GHistIndexMatrix is row-major) */
 } orc_ctx;
 
 void orc_ctx_destroy(orc_ctx* c) {
@@ -482,9 +483,10 @@ void orc_ctx_destroy(orc_ctx* c) {
     if (c->ncuts) free(c->ncuts[k]);
     if (c->min_vals) free(c->min_vals[k]);
     if (c->bins_col) free(c->bins_col[k]);
+    if (c->bins_row) free(c->bins_row[k]);
   }
   free(c->perm); free(c->fold_begin); free(c->ntrain); free(c->ntest);
-  free(c->train_rows); free(c->test_rows); free(c->cuts); free(c->ncuts); free(c->min_vals); free(c->bins_col);
+  free(c->train_rows); free(c->test_rows); free(c->cuts); free(c->ncuts); free(c->min_vals); free(c->bins_col); free(c->bins_row);
   free(c);
 }
 
@@ -508,6 +510,7 @@ orc_ctx* orc_ctx_create(const float* X, int64_t n, int32_t f, int64_t ldx, const
   c->ncuts = (int32_t**)calloc((size_t)nfold, sizeof(void*));
   c->min_vals = (float**)calloc((size_t)nfold, sizeof(void*));
   c->bins_col = (uint8_t**)calloc((size_t)nfold, sizeof(void*));
+  c->bins_row = (uint8_t**)calloc((size_t)nfold, sizeof(void*));
   for (int k = 0; k < nfold; ++k) {
     int64_t nt = c->fold_begin[k + 1] - c->fold_begin[k];
     int64_t ntr = n - nt;
@@ -530,11 +533,19 @@ orc_ctx* orc_ctx_create(const float* X, int64_t n, int32_t f, int64_t ldx, const
     const int64_t* tr = c->train_rows[k];
     uint8_t* bc = c->bins_col[k];
 #pragma omp parallel for schedule(static)
-    for (int j = 0; j < f; ++j) {
-      const float* cj = c->cuts[k] + (size_t)j * ORC_MAX_BIN;
-      int nc = c->ncuts[k][j];
-      for (int64_t r = 0; r < ntr; ++r) bc[(size_t)j * ntr + r] = orc_search_bin(cj, nc, X[tr[r] * ldx + j]);
+    for (int64_t r0 = 0; r0 < ntr; r0 += 4096) {   /* row blocks: every row of X is touched once */
+      const int64_t r1 = r0 + 4096 < ntr ? r0 + 4096 : ntr;
+      for (int j = 0; j < f; ++j) {
+        const float* cj = c->cuts[k] + (size_t)j * ORC_MAX_BIN;
+        int nc = c->ncuts[k][j];
+        for (int64_t r = r0; r < r1; ++r) bc[(size_t)j * ntr + r] = orc_search_bin(cj, nc, X[tr[r] * ldx + j]);
+      }
     }
+    c->bins_row[k] = (uint8_t*)malloc((size_t)f * (size_t)(ntr > 0 ? ntr : 1));
+    uint8_t* br = c->bins_row[k];
+#pragma omp parallel for schedule(static)
+    for (int64_t r = 0; r < ntr; ++r)
+      for (int j = 0; j < f; ++j) br[(size_t)r * f + j] = bc[(size_t)j * ntr + r];
   }
   return c;
 }
@@ -563,6 +574,91 @@ typedef struct {
 
 typedef struct { double g, h; } orc_gh;
 
+/* optional phase timers (ORC_PROFILE=1 prints them at the end of orc_cv) */
+static double orc_t_hist, orc_t_eval, orc_t_part, orc_t_sub, orc_t_grad, orc_t_pred;
+static double orc_now(void) {
+#ifdef _OPENMP
+  return omp_get_wtime();
+#else
+  return 0.0;
+#endif
+}
+
+/* Histogram accumulation is row-parallel in the way upstream's BuildHist is (common/hist_util.cc: blocks of rows,
+ * partial histograms, ordered reduction), but with a FIXED block size so that the result does not depend on the thread
+ * count: a node's rows are cut into blocks of ORC_HIST_BLOCK rows, every block is one task that adds its rows in
+ * row-set order into a partial histogram, and the partials of a node are summed in block order.  A node
+ * of at most ORC_HIST_BLOCK rows is therefore accumulated exactly as a sequential loop would. */
+#define ORC_HIST_BLOCK 16384
+/* histogram buffers are recycled (a 200 KB calloc per node is an mmap + page faults + munmap every time); only the
+ * serial parts of the tree loop take from / return to the pool */
+static orc_gh** orc_pool; static size_t orc_pool_n, orc_pool_cap, orc_pool_hsz;
+static orc_gh* orc_pool_get(size_t hsz) {
+  if (hsz != orc_pool_hsz) { while (orc_pool_n) free(orc_pool[--orc_pool_n]); orc_pool_hsz = hsz; }
+  if (orc_pool_n) return orc_pool[--orc_pool_n];
+  return (orc_gh*)malloc(hsz * sizeof(orc_gh));
+}
+static void orc_pool_put(orc_gh* p) {
+  if (!p) return;
+  if (orc_pool_n == orc_pool_cap) { orc_pool_cap = orc_pool_cap ? 2 * orc_pool_cap : 64; orc_pool = (orc_gh**)realloc(orc_pool, orc_pool_cap * sizeof(void*)); }
+  orc_pool[orc_pool_n++] = p;
+}
+static void orc_pool_release(void) { while (orc_pool_n) free(orc_pool[--orc_pool_n]); free(orc_pool); orc_pool = NULL; orc_pool_cap = 0; }
+typedef struct { int32_t node; int64_t begin, count; orc_gh* dst; } orc_hist_task;
+
+static void orc_build_hists(const orc_ctx* c, int k, const float* g, const float* h, const int64_t* cur,
+                            const orc_node* nodes, const int* build_ids, int n_build, orc_gh** hist_of_node) {
+  const int f = c->f;
+  const uint8_t* br = c->bins_row[k];
+  const size_t hsz = (size_t)f * ORC_MAX_BIN;
+  int64_t n_tasks = 0, n_extra = 0;
+  for (int q = 0; q < n_build; ++q) {
+    int64_t nb = (nodes[build_ids[q]].count + ORC_HIST_BLOCK - 1) / ORC_HIST_BLOCK; if (nb < 1) nb = 1;
+    n_tasks += nb; n_extra += nb - 1;
+  }
+  orc_hist_task* tasks = (orc_hist_task*)malloc(sizeof(orc_hist_task) * (size_t)(n_tasks > 0 ? n_tasks : 1));
+  orc_gh* extra = n_extra ? (orc_gh*)malloc((size_t)n_extra * hsz * sizeof(orc_gh)) : NULL;
+  int64_t t = 0, x = 0;
+  for (int q = 0; q < n_build; ++q) {
+    const orc_node* B = &nodes[build_ids[q]];
+    hist_of_node[build_ids[q]] = orc_pool_get(hsz);
+    int64_t nb = (B->count + ORC_HIST_BLOCK - 1) / ORC_HIST_BLOCK; if (nb < 1) nb = 1;
+    for (int64_t b = 0; b < nb; ++b) {
+      int64_t o = b * ORC_HIST_BLOCK, cnt = B->count - o < ORC_HIST_BLOCK ? B->count - o : ORC_HIST_BLOCK;
+      tasks[t].node = build_ids[q]; tasks[t].begin = B->begin + o; tasks[t].count = cnt < 0 ? 0 : cnt;
+      tasks[t].dst = b == 0 ? hist_of_node[build_ids[q]] : extra + (size_t)(x++) * hsz;
+      ++t;
+    }
+  }
+  /* row-wise accumulation (hist_util.cc RowsWiseBuildHistKernel): one pass over a block's rows, all features of a
+   * row together; each cell still receives its rows in row-set order */
+#pragma omp parallel for schedule(dynamic, 1)
+  for (int64_t ti = 0; ti < n_tasks; ++ti) {
+    orc_gh* H = tasks[ti].dst;
+    memset(H, 0, hsz * sizeof(orc_gh));
+    const int64_t* rs = cur + tasks[ti].begin; const int64_t cnt = tasks[ti].count;
+    for (int64_t i = 0; i < cnt; ++i) {
+      if (i + 8 < cnt) __builtin_prefetch(br + (size_t)rs[i + 8] * f);
+      const int64_t r = rs[i];
+      const double gi = g[r], hi = h[r];
+      const uint8_t* row = br + (size_t)r * f;
+      for (int j = 0; j < f; ++j) { orc_gh* cell = H + (size_t)j * ORC_MAX_BIN + row[j]; cell->g += gi; cell->h += hi; }
+    }
+  }
+  if (n_extra) {   /* partials of a node, in block order */
+#pragma omp parallel for schedule(static)
+    for (int j = 0; j < f; ++j)
+      for (int64_t ti = 0; ti < n_tasks; ++ti) {
+        orc_gh* H = hist_of_node[tasks[ti].node];
+        if (tasks[ti].dst == H) continue;
+        const orc_gh* src = tasks[ti].dst + (size_t)j * ORC_MAX_BIN; orc_gh* dj = H + (size_t)j * ORC_MAX_BIN;
+        for (int b = 0; b < ORC_MAX_BIN; ++b) { dj[b].g += src[b].g; dj[b].h += src[b].h; }
+      }
+    free(extra);
+  }
+  free(tasks);
+}
+
 /* one boosting round for one fold: grow a depthwise hist tree (updater_quantile_hist.cc UpdateTree,
  * hist/evaluate_splits.h HistEvaluator, hist/histogram.h subtraction trick, common/partition_builder.h). */
 static void orc_grow_tree(const orc_ctx* c, int k, const orc_params* p, int round,
@@ -586,19 +682,19 @@ static void orc_grow_tree(const orc_ctx* c, int k, const orc_params* p, int roun
   }
   int n_tree = 0; for (int j = 0; j < f; ++j) n_tree += tree_mask[j];
 
+#pragma omp parallel for schedule(static)
   for (int64_t r = 0; r < ntr; ++r) rows_a[r] = r;
   int64_t* cur = rows_a; int64_t* nxt = rows_b;
+  int* build_ids = (int*)malloc(sizeof(int) * 1024);
   /* root */
   orc_node* root = &nodes[0];
   root->state = 1; root->begin = 0; root->count = ntr;
-  hist_of_node[0] = (orc_gh*)calloc(hsz, sizeof(orc_gh));
   {
-    orc_gh* H0 = hist_of_node[0];
-#pragma omp parallel for schedule(static)
-    for (int j = 0; j < f; ++j) {
-      orc_gh* hj = H0 + (size_t)j * ORC_MAX_BIN; const uint8_t* col = bc + (size_t)j * ntr;
-      for (int64_t r = 0; r < ntr; ++r) { hj[col[r]].g += g[r]; hj[col[r]].h += h[r]; }
-    }
+    build_ids[0] = 0;
+    double t0 = orc_now();
+    orc_build_hists(c, k, g, h, cur, nodes, build_ids, 1, hist_of_node);
+    orc_t_hist += orc_now() - t0;
+    const orc_gh* H0 = hist_of_node[0];
     double G = 0, Hs = 0;   /* InitRoot: dense data -> sum of the first feature's histogram */
     for (int b = 0; b < ncuts[0]; ++b) { G += H0[b].g; Hs += H0[b].h; }
     root->G = G; root->H = Hs;
@@ -615,11 +711,13 @@ static void orc_grow_tree(const orc_ctx* c, int k, const orc_params* p, int roun
       orc_sample_features(orc_stream_key(3, (uint32_t)k, (uint32_t)round, (uint32_t)depth), tree_mask, f, nk, level_mask);
     }
     int any_open = 0;
-    /* EvaluateSplits for all open nodes on this level */
+    double t_ph = orc_now();
+    /* EvaluateSplits for all open nodes on this level (nodes are independent of each other) */
+#pragma omp parallel for schedule(dynamic, 1) reduction(| : any_open)
     for (int nid = first; nid < last; ++nid) {
       orc_node* nd = &nodes[nid];
       if (nd->state != 1) continue;
-      any_open = 1;
+      any_open |= 1;
       const orc_gh* Hn = hist_of_node[nid];
       float best_chg = 0.0f; int best_f = -1, best_b = -1; double best_GL = 0, best_HL = 0;
       for (int j = 0; j < f; ++j) {
@@ -647,56 +745,98 @@ static void orc_grow_tree(const orc_ctx* c, int k, const orc_params* p, int roun
       if (!valid) { nd->state = 3; continue; }
       nd->state = 2; nd->feat = best_f; nd->bin = best_b; nd->GL = best_GL; nd->HL = best_HL;
     }
+    orc_t_eval += orc_now() - t_ph; t_ph = orc_now();
     if (!any_open) break;
     /* ApplyTreeSplit + UpdatePosition (stable partition); rows of finished nodes stay where they are */
     int children_evaluated = (depth + 1 < D);  /* Driver::IsChildValid */
-    memcpy(nxt, cur, sizeof(int64_t) * (size_t)ntr);
+#pragma omp parallel for schedule(static)
+    for (int64_t q = 0; q < (ntr + 65535) / 65536; ++q) {
+      int64_t o = q * 65536, m = ntr - o < 65536 ? ntr - o : 65536;
+      memcpy(nxt + o, cur + o, sizeof(int64_t) * (size_t)m);
+    }
+    /* partition_builder.h: blocks of rows are counted in parallel, then scattered to their stable positions */
+    int64_t n_pt = 0;
+    for (int nid = first; nid < last; ++nid)
+      if (nodes[nid].state == 2) n_pt += (nodes[nid].count + ORC_HIST_BLOCK - 1) / ORC_HIST_BLOCK;
+    orc_hist_task* pt = (orc_hist_task*)malloc(sizeof(orc_hist_task) * (size_t)(n_pt > 0 ? n_pt : 1));
+    int64_t* pt_left = (int64_t*)malloc(sizeof(int64_t) * (size_t)(n_pt > 0 ? n_pt : 1));
+    n_pt = 0;
     for (int nid = first; nid < last; ++nid) {
+      if (nodes[nid].state != 2) continue;
+      for (int64_t o = 0; o < nodes[nid].count; o += ORC_HIST_BLOCK) {
+        pt[n_pt].node = nid; pt[n_pt].begin = nodes[nid].begin + o;
+        pt[n_pt].count = nodes[nid].count - o < ORC_HIST_BLOCK ? nodes[nid].count - o : ORC_HIST_BLOCK; pt[n_pt].dst = NULL;
+        ++n_pt;
+      }
+    }
+#pragma omp parallel for schedule(dynamic, 1)
+    for (int64_t ti = 0; ti < n_pt; ++ti) {
+      const orc_node* nd = &nodes[pt[ti].node];
+      const uint8_t* col = bc + (size_t)nd->feat * ntr;
+      int64_t nl = 0;
+      for (int64_t i = 0; i < pt[ti].count; ++i) nl += (col[cur[pt[ti].begin + i]] <= nd->bin);
+      pt_left[ti] = nl;
+    }
+    for (int64_t ti = 0; ti < n_pt;) {   /* per node: children, and each block's offset among the node's lefts */
+      const int nid = pt[ti].node;
       orc_node* nd = &nodes[nid];
-      if (nd->state != 2) continue;
+      int64_t tj = ti, nl = 0;
+      while (tj < n_pt && pt[tj].node == nid) { int64_t v = pt_left[tj]; pt_left[tj] = nl; nl += v; ++tj; }
       orc_node* L = &nodes[2 * nid + 1]; orc_node* R = &nodes[2 * nid + 2];
       L->G = nd->GL; L->H = nd->HL; R->G = nd->G - nd->GL; R->H = nd->H - nd->HL;
       L->weight = calc_weight(p, L->G, L->H); R->weight = calc_weight(p, R->G, R->H);
       L->root_gain = calc_gain(p, L->G, L->H); R->root_gain = calc_gain(p, R->G, R->H);
       L->state = R->state = children_evaluated ? 1 : 3;
+      L->begin = nd->begin; L->count = nl; R->begin = nd->begin + nl; R->count = nd->count - nl;
+      ti = tj;
+    }
+#pragma omp parallel for schedule(dynamic, 1)
+    for (int64_t ti = 0; ti < n_pt; ++ti) {
+      const orc_node* nd = &nodes[pt[ti].node];
       const uint8_t* col = bc + (size_t)nd->feat * ntr;
-      int64_t nl = 0;
-      for (int64_t i = 0; i < nd->count; ++i) nl += (col[cur[nd->begin + i]] <= nd->bin);
-      int64_t il = nd->begin, ir = nd->begin + nl;
-      for (int64_t i = 0; i < nd->count; ++i) {
-        int64_t r = cur[nd->begin + i];
+      const int64_t nl_node = nodes[2 * pt[ti].node + 1].count;
+      int64_t il = nd->begin + pt_left[ti];
+      int64_t ir = nd->begin + nl_node + ((pt[ti].begin - nd->begin) - pt_left[ti]);
+      for (int64_t i = 0; i < pt[ti].count; ++i) {
+        int64_t r = cur[pt[ti].begin + i];
         if (col[r] <= nd->bin) nxt[il++] = r; else nxt[ir++] = r;
       }
-      L->begin = nd->begin; L->count = nl; R->begin = nd->begin + nl; R->count = nd->count - nl;
     }
+    free(pt); free(pt_left);
     { int64_t* t = cur; cur = nxt; nxt = t; }
+    orc_t_part += orc_now() - t_ph; t_ph = orc_now();
     if (!children_evaluated) break;
     /* BuildHistogram: build the child with the smaller hessian sum, the sibling by subtraction */
+    int n_build = 0;
     for (int nid = first; nid < last; ++nid) {
-      orc_node* nd = &nodes[nid];
-      if (nd->state != 2) continue;
+      if (nodes[nid].state != 2) continue;
       int li = 2 * nid + 1, ri = 2 * nid + 2;
-      int fewer_right = nodes[ri].H < nodes[li].H;
-      int bi = fewer_right ? ri : li, si = fewer_right ? li : ri;
-      orc_gh* Hb = (orc_gh*)calloc(hsz, sizeof(orc_gh));
-      orc_gh* Hs = (orc_gh*)malloc(hsz * sizeof(orc_gh));
-      const orc_node* B = &nodes[bi];
-      const int64_t* rs = cur + B->begin; int64_t cnt = B->count;
-#pragma omp parallel for schedule(static)
-      for (int j = 0; j < f; ++j) {
-        orc_gh* hj = Hb + (size_t)j * ORC_MAX_BIN; const uint8_t* col = bc + (size_t)j * ntr;
-        for (int64_t i = 0; i < cnt; ++i) { int64_t r = rs[i]; hj[col[r]].g += g[r]; hj[col[r]].h += h[r]; }
-      }
-      const orc_gh* Hp = hist_of_node[nid];
-      for (size_t q = 0; q < hsz; ++q) { Hs[q].g = Hp[q].g - Hb[q].g; Hs[q].h = Hp[q].h - Hb[q].h; }
-      hist_of_node[bi] = Hb; hist_of_node[si] = Hs;
-      free(hist_of_node[nid]); hist_of_node[nid] = NULL;
+      build_ids[n_build++] = nodes[ri].H < nodes[li].H ? ri : li;
     }
+    orc_build_hists(c, k, g, h, cur, nodes, build_ids, n_build, hist_of_node);
+    orc_t_hist += orc_now() - t_ph; t_ph = orc_now();
+    for (int q = 0; q < n_build; ++q) {
+      int bi = build_ids[q], nid = (bi - 1) >> 1, si = bi == 2 * nid + 1 ? 2 * nid + 2 : 2 * nid + 1;
+      hist_of_node[si] = orc_pool_get(hsz);
+    }
+#pragma omp parallel for schedule(dynamic, 1)
+    for (int q = 0; q < n_build; ++q) {
+      int bi = build_ids[q], nid = (bi - 1) >> 1, si = bi == 2 * nid + 1 ? 2 * nid + 2 : 2 * nid + 1;
+      orc_gh* Hs = hist_of_node[si];
+      const orc_gh* Hb = hist_of_node[bi];
+      const orc_gh* Hp = hist_of_node[nid];
+      for (size_t q2 = 0; q2 < hsz; ++q2) { Hs[q2].g = Hp[q2].g - Hb[q2].g; Hs[q2].h = Hp[q2].h - Hb[q2].h; }
+    }
+    for (int q = 0; q < n_build; ++q) {
+      int nid = (build_ids[q] - 1) >> 1;
+      orc_pool_put(hist_of_node[nid]); hist_of_node[nid] = NULL;
+    }
+    orc_t_sub += orc_now() - t_ph;
   }
-  for (int i = 0; i < ORC_MAX_NODES; ++i) { if (hist_of_node[i]) { free(hist_of_node[i]); hist_of_node[i] = NULL; } }
+  for (int i = 0; i < ORC_MAX_NODES; ++i) { if (hist_of_node[i]) { orc_pool_put(hist_of_node[i]); hist_of_node[i] = NULL; } }
   /* the final row sets are in `cur`; make sure rows_a holds them for the caller */
   if (cur != rows_a) memcpy(rows_a, cur, sizeof(int64_t) * (size_t)ntr);
-  free(all_mask); free(tree_mask); free(level_mask);
+  free(all_mask); free(tree_mask); free(level_mask); free(build_ids);
 }
 
 typedef struct {
@@ -771,6 +911,7 @@ int orc_cv(const orc_ctx* c, const double* genes, const orc_opts* o, orc_result*
       int64_t ntr = c->ntrain[k], nte = c->ntest[k];
       /* X4: RegLossObj::GetGradient (src/objective/regression_obj.cu) */
       uint64_t skey = orc_stream_key(1, (uint32_t)k, (uint32_t)it, 0);
+#pragma omp parallel for schedule(static)
       for (int64_t r = 0; r < ntr; ++r) {
         float yy = ytr[k][r];
         float w = (yy == 1.0f) ? p.spw : 1.0f;
@@ -793,6 +934,7 @@ int orc_cv(const orc_ctx* c, const double* genes, const orc_opts* o, orc_result*
         if (final_rows && it == trees_rounds - 1) memcpy(final_rows + (size_t)k * (size_t)final_rows_stride, rows_a, sizeof(int64_t) * (size_t)ntr);
       }
       /* X8: UpdatePredictionCache -- every train row gets the leaf it ended in */
+#pragma omp parallel for schedule(dynamic, 1)
       for (int i = 0; i < ORC_MAX_NODES; ++i) {
         if (nodes[i].state != 3) continue;
         /* every leaf owns the segment [begin, begin+count) of the final row set */
@@ -840,6 +982,9 @@ int orc_cv(const orc_ctx* c, const double* genes, const orc_opts* o, orc_result*
     }
   }
   if (o->early_stopping_rounds <= 0) { best_iter = rounds_run - 1; }
+  if (getenv("ORC_PROFILE"))
+    fprintf(stderr, "orc_cv phases (s): hist %.3f eval %.3f partition %.3f subtract %.3f\n", orc_t_hist, orc_t_eval, orc_t_part, orc_t_sub);
+  orc_t_hist = orc_t_eval = orc_t_part = orc_t_sub = orc_t_grad = orc_t_pred = 0;
   res->rounds_run = rounds_run; res->best_iteration = best_iter; res->stopped_early = stopped;
   /* cv() truncates the table to best_iteration+1 rows when stopping fired; gentun takes the last row */
   res->fitness = stopped ? means[best_iter] : last_mean;
@@ -847,6 +992,7 @@ int orc_cv(const orc_ctx* c, const double* genes, const orc_opts* o, orc_result*
   for (int k = 0; k < nfold; ++k) { free(ptr[k]); free(pte[k]); free(ytr[k]); free(yte[k]); }
   free(ptr); free(pte); free(ytr); free(yte); free(g); free(h); free(rows_a); free(rows_b);
   free(nodes); free(hist_of_node); free(leaf_of_node); free(means);
+  orc_pool_release();
   return 0;
 }
 
@@ -858,6 +1004,24 @@ int orc_cross_validate(const float* X, int64_t n, int32_t f, int64_t ldx, const 
   int rc = orc_cv(c, genes, o, res, NULL, NULL, 0, NULL, 0);
   orc_ctx_destroy(c);
   return rc;
+}
+
+/* threads a parallel region really gets when `nthread` is asked for (0 = the OpenMP default): launchers such as
+ * torch.distributed.run export OMP_NUM_THREADS=1, so the CPU baseline passes its core count explicitly and reports this */
+int orc_threads_in_use(int nthread) {
+#ifdef _OPENMP
+  if (nthread > 0) omp_set_num_threads(nthread);
+  int n = 1;
+#pragma omp parallel
+  {
+#pragma omp single
+    n = omp_get_num_threads();
+  }
+  return n;
+#else
+  (void)nthread;
+  return 1;
+#endif
 }
 
 int orc_max_threads(void) {

@@ -66,6 +66,8 @@ def lib():
                                          C.POINTER(Opts), C.POINTER(Result)]
         L.orc_make_folds.argtypes = [C.c_int64, C.c_int32, C.c_uint32, C.c_void_p, C.c_void_p]
         L.orc_max_threads.restype = C.c_int
+        L.orc_threads_in_use.restype = C.c_int
+        L.orc_threads_in_use.argtypes = [C.c_int]
         _lib = L
     return _lib
 
@@ -185,3 +187,16 @@ def cross_validate(x, y, genes, nthread=0, **additional_parameters):
 
 def max_threads():
     return lib().orc_max_threads()
+
+
+def host_cores():
+    """Cores this process may run on (the affinity mask, not what OMP_NUM_THREADS says)."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def threads_in_use(nthread=0):
+    """Threads an OpenMP region of the oracle really runs with when `nthread` is requested."""
+    return lib().orc_threads_in_use(int(nthread))
