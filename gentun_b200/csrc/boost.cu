@@ -436,10 +436,16 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 2 : 1) k_
   constexpr int kGroupsPerCta = UNITS / 2;
   constexpr uint32_t kStride = (kThreads / 32) * 32u;          // rows per CTA iteration
   constexpr int kEpochIters = kEpochRows / (int)kStride;       // CTA iterations between overflow checks
-  const int j = blockIdx.y;
-  const JobState& js = w.js[j];
+  // Grid: x = (job, feature-group slice), y = work item, and x enumerates the level's jobs fold-major (all
+  // individuals of fold 0, then fold 1, ...).  CTAs are dispatched x-fastest, so the CTAs in flight at one time are
+  // the SAME item index of many jobs of ONE fold: at the top levels (row sets still near the identity) they read the
+  // same bin rows, which then come from L2 for all but the first of them.
   const int ncg = w.groups / kGroupsPerCta;
-  const int item_idx = blockIdx.x / ncg, cg = blockIdx.x % ncg;
+  const int lvl_jobs = (int)gridDim.x / ncg, lvl_inds = lvl_jobs / w.nfold;
+  const int jx = (int)blockIdx.x / ncg, cg = (int)blockIdx.x % ncg;
+  const int j = (jx % lvl_inds) * w.nfold + jx / lvl_inds;
+  const JobState& js = w.js[j];
+  const int item_idx = blockIdx.y;
   if (item_idx >= js.n_hist_items) return;
   const JobParams& jp = w.jp[j];
   const HistItem it = w.hitems[(size_t)j * w.hist_cap + item_idx];
@@ -479,7 +485,13 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 2 : 1) k_
   row_b = row_c;
   const uint32_t n_iter = (cnt + kStride - 1) / kStride;   // CTA-uniform trip count
   unsigned acc_g = 0u, acc_h = 0u, abs_rows = 0u;   // abs_rows: this lane's share of the node's sum of |g_q| (< 2^27 per item)
-  unsigned run_g = 0u, run_h = 0u;                  // this warp's sums since the CTA's last flush
+  unsigned run_g = 0u, run_h = 0u;                  // this warp's sums since the CTA last looked at its cells
+  constexpr unsigned kWarps = kThreads / 32;
+  // what a warp may add before the CTA has to look: an equal share of what the int32 range leaves above the largest
+  // cell seen at the last look, less a worst-case epoch
+  unsigned lim_g = (0x7fffffffu - ((unsigned)kEpochRows << kQuantBits)) / kWarps;
+  unsigned lim_h = (0x7fffffffu - ((unsigned)kEpochRows << kQuantBitsH)) / kWarps;
+  __shared__ unsigned s_cellmax[kWarps];
   for (uint32_t itn = 0; itn < n_iter; ++itn) {
     const uint32_t p2 = my0 + (itn + 2) * kStride;
     row_c = p2 < cnt ? ridx[p2] : 0xffffffffu;
@@ -502,13 +514,29 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 2 : 1) k_
       run_h += __reduce_add_sync(0xffffffffu, acc_h);
       abs_rows += acc_g;
       acc_g = 0u; acc_h = 0u;
-      constexpr unsigned kWarps = kThreads / 32;
-      constexpr unsigned lim_g = (0x7fffffffu - ((unsigned)kEpochRows << kQuantBits)) / kWarps;
-      constexpr unsigned lim_h = (0x7fffffffu - ((unsigned)kEpochRows << kQuantBitsH)) / kWarps;
       const bool must = __syncthreads_or((run_g >= lim_g || run_h >= lim_h) && !never_early);
       if (must) {
-        hist_flush<UNITS>(w, jp, level, it, cg, sh, shared_node ? kFlushAtomic : stored ? kFlushAddWide : kFlushStoreWide, true);
-        stored = true;
+        // The running sums bound every cell as if all rows had fallen into one bin.  Look at the cells themselves:
+        // with rows spread over many bins the largest one is far below the bound, and the CTA carries on from there
+        // instead of flushing (a flush is ~65 000 global atomics, a look is one pass over shared memory).
+        unsigned m = 0u;
+        for (int i = threadIdx.x; i < kGroupsPerCta * 2 * kBins * kLanes / 4; i += kThreads) {
+          const int4 v = reinterpret_cast<const int4*>(sh)[i];
+          m = max(max(m, (unsigned)abs(v.x)), max((unsigned)abs(v.y), max((unsigned)abs(v.z), (unsigned)abs(v.w))));
+        }
+        m = __reduce_max_sync(0xffffffffu, m);
+        if (lane == 0) s_cellmax[wid] = m;
+        __syncthreads();
+        m = 0u;
+#pragma unroll
+        for (unsigned q = 0; q < kWarps; ++q) m = max(m, s_cellmax[q]);
+        if (m >= 0x40000000u) {
+          hist_flush<UNITS>(w, jp, level, it, cg, sh, shared_node ? kFlushAtomic : stored ? kFlushAddWide : kFlushStoreWide, true);
+          stored = true;
+          m = 0u;
+        }
+        lim_g = (0x7fffffffu - m - ((unsigned)kEpochRows << kQuantBits)) / kWarps;
+        lim_h = (0x7fffffffu - m - ((unsigned)kEpochRows << kQuantBitsH)) / kWarps;
         run_g = 0u; run_h = 0u;
         __syncthreads();
       }
@@ -1743,8 +1771,8 @@ void launch_plan_hist(const Wave& w, int level, cudaStream_t s) { k_plan_hist<<<
 void launch_hist_zero(const Wave& w, int level, cudaStream_t s) { k_hist_zero<<<dim3(32, w.lvl_jobs[level]), 256, 0, s>>>(w, level); }
 int launch_hist(const Wave& w, int level, cudaStream_t s) {   // returns the number of kernels launched
   int cap = hist_items_bound(w, level);
-  if (w.groups % 2 == 0) k_hist<4><<<dim3(cap * (w.groups / 2), w.lvl_jobs[level]), 512, 2 * kHistSmem, s>>>(w, level);
-  else k_hist<2><<<dim3(cap * w.groups, w.lvl_jobs[level]), 256, kHistSmem, s>>>(w, level);
+  if (w.groups % 2 == 0) k_hist<4><<<dim3(w.lvl_jobs[level] * (w.groups / 2), cap), 512, 2 * kHistSmem, s>>>(w, level);
+  else k_hist<2><<<dim3(w.lvl_jobs[level] * w.groups, cap), 256, kHistSmem, s>>>(w, level);
   return 1;
 }
 int launch_scan(const Wave& w, int level, cudaStream_t s) {   // returns the number of kernels launched

@@ -9,7 +9,10 @@ constexpr int kBins = 256;          // max_bin (xgboost default, never overridde
 constexpr int kLanes = 32;          // features per histogram group == smem banks
 constexpr int kMaxDepth = 10;       // max_depth gene range 3..10 (gentun/individuals.py:167)
 constexpr int kNodeCap = 2048;      // heap slots per tree (2^(10+1)-1 used)
-constexpr int kHistRows = 16384;    // rows per histogram work item
+#ifndef GT_HIST_ROWS
+#define GT_HIST_ROWS 16384
+#endif
+constexpr int kHistRows = GT_HIST_ROWS;   // rows per histogram work item
 constexpr int kEpochRows = 2048;    // rows between int32-overflow checks of the shared partial sums
 constexpr int kNarrowRows = 4095;   // nodes up to this many rows keep int32 histogram cells whatever their gradients: 4095 * 2^19 < 2^31
 #ifndef GT_PART_ROWS
