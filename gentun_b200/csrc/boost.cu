@@ -273,12 +273,12 @@ __global__ void __launch_bounds__(256) k_plan_hist(Wave w, int level) {
     if (bnode[s2] < 0) continue;
     const Node& bn = nodes[bnode[s2]];
     for (int c = 0; c < chunks[s2]; ++c, ++ni) {
-      if (ni >= w.hist_cap) break;
+      if (ni >= w.hist_cap) { w.counters[7] = 1ull; break; }   // never expected (the cap is an upper bound); reported, not ignored
       const uint32_t b = (uint32_t)c * kHistRows;
       const uint32_t cnt = bn.cnt > b ? (bn.cnt - b < (uint32_t)kHistRows ? bn.cnt - b : (uint32_t)kHistRows) : 0u;
       items[ni] = HistItem{bnode[s2], bn.begin + b, cnt, shr[s2] | ((int)bn.buf << 1)};
     }
-    if (shr[s2]) { if (nz < w.hist_cap) zl[nz] = bnode[s2]; ++nz; }
+    if (shr[s2]) { if (nz < w.hist_cap) zl[nz] = bnode[s2]; else w.counters[7] = 1ull; ++nz; }
     pairs[np] = level == 0 ? PairRec{-1, 0, 1, j} : PairRec{(bnode[s2] - 1) >> 1, (bnode[s2] & 1) ? 0 : 1, single[s2], j};
     ++np;
     rows_mine += bn.cnt;
@@ -1222,7 +1222,7 @@ __global__ void __launch_bounds__(256) k_plan_part(Wave w, int level) {
     const Node& nd = nodes[nid[s2]];
     const int first_item = ni;
     for (int c = 0; c < chunks[s2]; ++c, ++ni) {
-      if (ni >= w.part_cap) break;
+      if (ni >= w.part_cap) { w.counters[7] = 2ull; break; }
       const uint32_t b = (uint32_t)c * kPartRows;
       const uint32_t cnt = nd.cnt - b < (uint32_t)kPartRows ? nd.cnt - b : (uint32_t)kPartRows;
       items[ni] = PartItem{nid[s2], nd.begin + b, cnt, first_item, chunks[s2], nd.begin, nd.cnt, (int)nd.buf};

@@ -124,7 +124,7 @@ struct Wave {            // passed by value to kernels
   uint32_t* pflags;      // [n_jobs][part_cap][kPartRows / 32] goes-left bit of every row of a partition item
   double* mpart;         // [n_jobs][pred_chunks] per-CTA metric partial sums
   double* trace;         // [n_inds][num_boost_round] or null
-  unsigned long long* counters;  // [0] rows through hist, [1] node histograms built, [2] active individuals, [5 + level parity] pairs of the level
+  unsigned long long* counters;  // [0] rows through hist, [1] node histograms built, [2] active individuals, [5 + level parity] pairs of the level, [7] work-list overflow (an error)
 };
 
 // counter-based generator (definition shared with the oracle by specification)

@@ -11,6 +11,7 @@
 #include <cstring>
 #include <map>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -175,6 +176,7 @@ int prepare_impl(gt_engine* e, int nfold, FoldSet** out) {
   fs->sum_not1_sq.assign(nfold, 0); fs->sum_not1_lg.assign(nfold, 0); fs->n1.assign(nfold, 0); fs->nnot1.assign(nfold, 0);
   cudaEvent_t ev0, ev1;
   GT_CUDA(cudaEventCreate(&ev0)); GT_CUDA(cudaEventCreate(&ev1));
+  struct EventGuard { cudaEvent_t a, b; ~EventGuard() { cudaEventDestroy(a); cudaEventDestroy(b); } } ev_guard{ev0, ev1};
   GT_CUDA(cudaEventRecord(ev0, e->stream));
   std::vector<const uint32_t*> h_row_ptrs(nfold);
   std::vector<long long> h_ntrain(nfold);
@@ -278,7 +280,6 @@ int prepare_impl(gt_engine* e, int nfold, FoldSet** out) {
   GT_CUDA(cudaStreamSynchronize(e->stream));
   float ms = 0;
   GT_CUDA(cudaEventElapsedTime(&ms, ev0, ev1));
-  cudaEventDestroy(ev0); cudaEventDestroy(ev1);
   fs->prepare_ms = ms;
   e->stats.prepare_ms = ms;
   *out = fs.get();
@@ -429,6 +430,10 @@ int eval_impl(gt_engine* e, int n_ind, const double* genes, const gt_fit_opts* o
   long long launches = 0, hist_launches = 0;
   cudaEvent_t e0, e1;
   GT_CUDA(cudaEventCreate(&e0)); GT_CUDA(cudaEventCreate(&e1));
+  struct EventGuard {   // every early return below releases the events
+    cudaEvent_t a, b; std::vector<cudaEvent_t>* more;
+    ~EventGuard() { cudaEventDestroy(a); cudaEventDestroy(b); for (auto x : *more) cudaEventDestroy(x); }
+  } ev_guard{e0, e1, &ev};
   GT_CUDA(cudaEventRecord(e0, e->stream));
   auto drain_events = [&]() {
     for (size_t q = 0; q + 1 < ev_used; q += 2) { float ms = 0; cudaEventElapsedTime(&ms, ev[q], ev[q + 1]); hist_ms += ms; }
@@ -567,8 +572,6 @@ int eval_impl(gt_engine* e, int n_ind, const double* genes, const gt_fit_opts* o
   if (rounds_out) for (int i = 0; i < n_ind; ++i) rounds_out[i] = h_rounds[i];
   float ms = 0;
   GT_CUDA(cudaEventElapsedTime(&ms, e0, e1));
-  cudaEventDestroy(e0); cudaEventDestroy(e1);
-  for (auto x : ev) cudaEventDestroy(x);
   e->stats.eval_ms = ms;
   e->stats.hist_ms = hist_ms;
   e->stats.hist_launches = hist_launches;
@@ -579,8 +582,10 @@ int eval_impl(gt_engine* e, int n_ind, const double* genes, const gt_fit_opts* o
   // + one F x 256 x 16 B histogram written per built node
   e->stats.hist_row_features = (double)h_counters[0] * (double)e->f;
   e->stats.hist_alg_bytes = (double)h_counters[0] * ((double)e->f + 12.0) + (double)h_counters[1] * (double)e->f * 256.0 * 16.0;
-  for (int i = 0; i < n_ind; ++i)
-    if (!std::isfinite(fitness_out[i])) return fail(GT_ERR_STATE, "individual %d produced a non-finite fitness", i);
+  if (h_counters[7])
+    return fail(GT_ERR_STATE, "%s work-item list overflowed its capacity: results of this call are void", h_counters[7] == 1 ? "histogram" : "partition");
+  // A non-finite fitness (xgboost would hand back nan / inf for that individual) is left in fitness_out for the caller
+  // to see; the other individuals' values stand.
   return GT_OK;
 }
 
@@ -590,11 +595,70 @@ namespace gt {
 void set_error_message(const char* msg) { g_err = msg ? msg : ""; }
 }  // namespace gt
 
-extern "C" {
+namespace {
 
-int gt_engine_create(const float* X, int64_t n, int32_t f, int64_t ldx, const float* y, const gt_data_opts* opts,
-                     gt_engine** out) {
-  if (!X || !y || !out || n < 2 || f < 1 || ldx < f) return fail(GT_ERR_ARG, "bad data arguments");
+// Host matrix as the caller holds it: element type, strides in elements (one of them 1).
+struct HostMatrix { const void* p; int dtype; int64_t row_stride, col_stride; };
+
+// Pinned staging buffers, kept for the life of the process (allocating pinned memory costs milliseconds per call and
+// the GA makes an engine per dataset, not per individual).  One ingestion at a time uses them.
+struct PinnedStage {
+  std::mutex mu;
+  void* buf[2] = {nullptr, nullptr};
+  static constexpr size_t kBytes = 16u << 20;
+  cudaError_t ensure() {
+    for (int b = 0; b < 2; ++b)
+      if (!buf[b]) { cudaError_t e = cudaHostAlloc(&buf[b], kBytes, cudaHostAllocDefault); if (e != cudaSuccess) return e; }
+    return cudaSuccess;
+  }
+};
+PinnedStage g_stage;
+
+// X (host, any supported type / layout) -> e->own_X (device, float, row-major [n][f]): tiles of rows go through the two
+// pinned buffers, so the host-side gather of tile t+1 overlaps the DMA and the cast kernel of tile t.
+int ingest_matrix(gt_engine* e, const HostMatrix& m) {
+  const int64_t n = e->n; const int f = e->f;
+  const size_t esz = m.dtype == GT_DTYPE_F64 ? 8 : 4;
+  const bool colmajor = m.row_stride == 1 && m.col_stride != 1;
+  std::lock_guard<std::mutex> lock(g_stage.mu);
+  GT_CUDA(g_stage.ensure());
+  const int64_t row_elems = colmajor ? f : m.row_stride;   // elements a tile holds per row
+  int64_t R = (int64_t)(PinnedStage::kBytes / ((size_t)row_elems * esz)) / 32 * 32;
+  if (R < 32) return fail(GT_ERR_ARG, "row stride %lld too large to stage", (long long)m.row_stride);
+  if (R > n) R = n;
+  DevBuf<unsigned char> d_tile[2];
+  cudaEvent_t done[2];
+  for (int b = 0; b < 2; ++b) { GT_CUDA(d_tile[b].ensure(PinnedStage::kBytes)); GT_CUDA(cudaEventCreateWithFlags(&done[b], cudaEventDisableTiming)); }
+  int rc = GT_OK;
+  int64_t t = 0;
+  for (int64_t r0 = 0; r0 < n && rc == GT_OK; r0 += R, ++t) {
+    const int b = (int)(t & 1);
+    const int64_t rows = std::min<int64_t>(R, n - r0);
+    if (t >= 2 && cudaEventSynchronize(done[b]) != cudaSuccess) { rc = fail(GT_ERR_CUDA, "staging event failed"); break; }
+    unsigned char* pin = (unsigned char*)g_stage.buf[b];
+    size_t bytes;
+    if (colmajor) {   // tile = [f][rows]
+      for (int c = 0; c < f; ++c)
+        memcpy(pin + (size_t)c * rows * esz, (const unsigned char*)m.p + ((size_t)c * m.col_stride + (size_t)r0) * esz, (size_t)rows * esz);
+      bytes = (size_t)f * rows * esz;
+    } else {          // tile = [rows][row_stride]
+      bytes = ((size_t)(rows - 1) * m.row_stride + f) * esz;
+      memcpy(pin, (const unsigned char*)m.p + (size_t)r0 * m.row_stride * esz, bytes);
+    }
+    cudaError_t ce = cudaMemcpyAsync(d_tile[b].p, pin, bytes, cudaMemcpyHostToDevice, e->stream);
+    if (ce != cudaSuccess) { rc = fail(GT_ERR_CUDA, "H2D of a staged tile failed: %s", cudaGetErrorString(ce)); break; }
+    gt::launch_ingest_tile(d_tile[b].p, m.dtype, colmajor ? 1 : 0, colmajor ? rows : m.row_stride, (int)rows, f, e->own_X.p, e->ldx, r0, e->stream);
+    cudaEventRecord(done[b], e->stream);
+  }
+  cudaError_t ce = cudaStreamSynchronize(e->stream);
+  for (int b = 0; b < 2; ++b) cudaEventDestroy(done[b]);
+  if (rc == GT_OK && ce != cudaSuccess) rc = fail(GT_ERR_CUDA, "ingestion failed: %s", cudaGetErrorString(ce));
+  return rc;
+}
+
+int create_impl(const HostMatrix* hm, const float* X_dev_or_null, int64_t n, int32_t f, int64_t ldx, const void* y, int y_dtype,
+                const gt_data_opts* opts, gt_engine** out) {
+  if (!y || !out || n < 2 || f < 1) return fail(GT_ERR_ARG, "bad data arguments");
   if (f > 256) return fail(GT_ERR_ARG, "f=%d exceeds 256 features", f);
   if (n >= (1ll << 31)) return fail(GT_ERR_ARG, "n=%lld exceeds 2^31 rows", (long long)n);
   int count = 0;
@@ -611,17 +675,24 @@ int gt_engine_create(const float* X, int64_t n, int32_t f, int64_t ldx, const fl
   e->groups = e->fpad / gt::kLanes;
   GT_CUDA(cudaSetDevice(e->device));
   GT_CUDA(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+  struct StreamGuard {   // the stream dies with a failed create
+    gt_engine* e; bool armed = true;
+    ~StreamGuard() { if (armed && e->stream) { cudaStreamDestroy(e->stream); e->stream = nullptr; } }
+  } guard{e.get()};
   e->h_y.resize(n);
-  if (opts && opts->x_on_device) {
-    e->d_X = X; e->d_y = y;
+  if (!hm) {
+    e->d_X = X_dev_or_null; e->d_y = (const float*)y;
     GT_CUDA(cudaMemcpy(e->h_y.data(), y, sizeof(float) * n, cudaMemcpyDeviceToHost));
   } else {
+    if (y_dtype == GT_DTYPE_F32) memcpy(e->h_y.data(), y, sizeof(float) * n);
+    else if (y_dtype == GT_DTYPE_F64) for (int64_t i = 0; i < n; ++i) e->h_y[i] = (float)((const double*)y)[i];
+    else if (y_dtype == GT_DTYPE_I64) for (int64_t i = 0; i < n; ++i) e->h_y[i] = (float)((const int64_t*)y)[i];
+    else return fail(GT_ERR_ARG, "unknown label type %d", y_dtype);
     GT_CUDA(e->own_X.ensure((size_t)n * ldx));
     GT_CUDA(e->own_y.ensure(n));
-    GT_CUDA(cudaMemcpyAsync(e->own_X.p, X, sizeof(float) * (size_t)n * ldx, cudaMemcpyHostToDevice, e->stream));
-    GT_CUDA(cudaMemcpyAsync(e->own_y.p, y, sizeof(float) * n, cudaMemcpyHostToDevice, e->stream));
-    GT_CUDA(cudaStreamSynchronize(e->stream));
-    memcpy(e->h_y.data(), y, sizeof(float) * n);
+    GT_CUDA(cudaMemcpyAsync(e->own_y.p, e->h_y.data(), sizeof(float) * n, cudaMemcpyHostToDevice, e->stream));
+    int rc = ingest_matrix(e.get(), *hm);
+    if (rc != GT_OK) return rc;
     e->d_X = e->own_X.p; e->d_y = e->own_y.p;
   }
   {
@@ -632,14 +703,36 @@ int gt_engine_create(const float* X, int64_t n, int32_t f, int64_t ldx, const fl
     gt::launch_count_nonfinite(e->d_X, n, f, ldx, e->d_y, d_bad.p, e->stream);
     GT_CUDA(cudaMemcpyAsync(h_bad, d_bad.p, sizeof(h_bad), cudaMemcpyDeviceToHost, e->stream));
     GT_CUDA(cudaStreamSynchronize(e->stream));
-    if (h_bad[0] || h_bad[1]) {
-      cudaStreamDestroy(e->stream);
+    if (h_bad[0] || h_bad[1])
       return fail(GT_ERR_ARG, "%llu values of X and %llu labels are NaN or inf: xgb.DMatrix would treat NaN as missing and refuse inf; "
                   "this engine has no missing-value path", h_bad[0], h_bad[1]);
-    }
   }
+  guard.armed = false;
   *out = e.release();
   return GT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int gt_engine_create(const float* X, int64_t n, int32_t f, int64_t ldx, const float* y, const gt_data_opts* opts,
+                     gt_engine** out) {
+  if (!X || ldx < f) return fail(GT_ERR_ARG, "bad data arguments");
+  if (opts && opts->x_on_device) return create_impl(nullptr, X, n, f, ldx, y, GT_DTYPE_F32, opts, out);
+  const HostMatrix hm{X, GT_DTYPE_F32, ldx, 1};
+  return create_impl(&hm, nullptr, n, f, f, y, GT_DTYPE_F32, opts, out);
+}
+
+int gt_engine_create_from(const void* X, int32_t x_dtype, int64_t n, int32_t f, int64_t x_row_stride, int64_t x_col_stride,
+                          const void* y, int32_t y_dtype, const gt_data_opts* opts, gt_engine** out) {
+  if (!X) return fail(GT_ERR_ARG, "bad data arguments");
+  if (opts && opts->x_on_device) return fail(GT_ERR_ARG, "gt_engine_create_from takes host arrays");
+  if (x_dtype != GT_DTYPE_F32 && x_dtype != GT_DTYPE_F64) return fail(GT_ERR_ARG, "unknown matrix element type %d", x_dtype);
+  const bool rowmajor = x_col_stride == 1 && x_row_stride >= f, colmajor = x_row_stride == 1 && x_col_stride >= n;
+  if (!rowmajor && !colmajor) return fail(GT_ERR_ARG, "matrix must be row-major or column-major (strides %lld, %lld)", (long long)x_row_stride, (long long)x_col_stride);
+  const HostMatrix hm{X, x_dtype, rowmajor ? x_row_stride : 1, rowmajor ? 1 : x_col_stride};
+  return create_impl(&hm, nullptr, n, f, f, y, y_dtype, opts, out);
 }
 
 int gt_engine_prepare(gt_engine* e, int32_t nfold) {

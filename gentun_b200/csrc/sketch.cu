@@ -651,6 +651,43 @@ static __global__ void k_count_nonfinite(const float* X, long long n, int f, lon
 void launch_count_nonfinite(const float* X, long long n, int f, long long ldx, const float* y, unsigned long long* out, cudaStream_t s) {
   k_count_nonfinite<<<148 * 8, 256, 0, s>>>(X, n, f, ldx, y, out);
 }
+// Ingestion of the caller's matrix as it lies in host memory (gt_engine_create_from): a tile of `rows` rows arrives
+// on the device in the caller's element type, either row-major (tile[r * ld + c]) or column-major (tile[c * ld + r],
+// how pandas keeps a float64 DataFrame); it is converted to float (the cast xgb.DMatrix applies) and written row-major.
+template <typename T, bool COLMAJOR>
+static __global__ void __launch_bounds__(256) k_ingest_tile(const T* __restrict__ tile, long long ld, int rows, int f,
+                                                            float* __restrict__ X, long long ldx, long long r0) {
+  __shared__ float s_t[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8
+  const int rb = blockIdx.x * 32, cb = blockIdx.y * 32;
+  if (COLMAJOR) {
+    for (int q = ty; q < 32; q += 8) {   // read along rows (contiguous in a column-major tile)
+      const int c = cb + q, r = rb + tx;
+      s_t[q][tx] = (c < f && r < rows) ? (float)tile[(long long)c * ld + r] : 0.f;
+    }
+    __syncthreads();
+    for (int q = ty; q < 32; q += 8) {   // write along columns
+      const int r = rb + q, c = cb + tx;
+      if (r < rows && c < f) X[(r0 + r) * ldx + c] = s_t[tx][q];
+    }
+  } else {
+    for (int q = ty; q < 32; q += 8) {
+      const int r = rb + q, c = cb + tx;
+      if (r < rows && c < f) X[(r0 + r) * ldx + c] = (float)tile[(long long)r * ld + c];
+    }
+  }
+}
+void launch_ingest_tile(const void* tile, int dtype, int colmajor, long long ld, int rows, int f, float* X, long long ldx,
+                        long long r0, cudaStream_t s) {
+  const dim3 grid((rows + 31) / 32, (f + 31) / 32);
+  if (dtype == GT_DTYPE_F64) {
+    if (colmajor) k_ingest_tile<double, true><<<grid, 256, 0, s>>>((const double*)tile, ld, rows, f, X, ldx, r0);
+    else k_ingest_tile<double, false><<<grid, 256, 0, s>>>((const double*)tile, ld, rows, f, X, ldx, r0);
+  } else {
+    if (colmajor) k_ingest_tile<float, true><<<grid, 256, 0, s>>>((const float*)tile, ld, rows, f, X, ldx, r0);
+    else k_ingest_tile<float, false><<<grid, 256, 0, s>>>((const float*)tile, ld, rows, f, X, ldx, r0);
+  }
+}
 void launch_gather_y(const float* y, const uint32_t* rows, long long n, float* out, cudaStream_t s) {
   int blocks = (int)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
   if (blocks < 1) blocks = 1;

@@ -119,13 +119,18 @@ class GentunWorker(object):
     waiting in the queue are taken `batch_size` at a time and trained together on this box's GPU(s)."""
 
     def __init__(self, individual, x_train, y_train, host='localhost', port=5672,
-                 user='guest', password='guest', rabbit_queue='rpc_queue', batch_size=64, batch_wait=0.05):
+                 user='guest', password='guest', rabbit_queue='rpc_queue', batch_size=64, batch_wait=0.05,
+                 heartbeat_every=1.0):
+        """batch_size is also the prefetch count: with several workers on one queue a large value lets the first
+        worker take jobs the others could have trained meanwhile, so size it to about pending / workers."""
         self.individual = individual
         self.x_train = x_train
         self.y_train = y_train
         self.rabbit_queue = rabbit_queue
         self.batch_size = batch_size
         self.batch_wait = batch_wait
+        self.heartbeat_every = heartbeat_every
+        self.heartbeats_served = 0
         self._pika, self.connection, self.channel = _connect(host, port, user, password)
         self.channel.queue_declare(queue=self.rabbit_queue)
 
@@ -138,13 +143,34 @@ class GentunWorker(object):
         return i, individual_class(x, y, genes=genes, **additional_parameters)
 
     def _evaluate(self, individuals):
+        """Train the batch on a helper thread while this thread, which owns the connection, keeps serving the broker's
+        heartbeats (the reference runs a heartbeat thread for the same reason, worker.py:26-33): a batch of default
+        5000-round fits can outlast the heartbeat timeout, and a dropped connection means the jobs are redelivered and
+        trained again.  The ctypes call releases the GIL, so the two threads do not get in each other's way."""
+        import threading
         from .population import _batch_hook
         hook = _batch_hook(self.individual)
-        if hook is not None:
-            hook(individuals)
-        else:
-            for ind in individuals:
-                ind.get_fitness()
+        failure = []
+
+        def train():
+            try:
+                if hook is not None:
+                    hook(individuals)
+                else:
+                    for ind in individuals:
+                        ind.get_fitness()
+            except BaseException as exc:   # re-raised on the connection's thread
+                failure.append(exc)
+
+        t = threading.Thread(target=train, name="gentun-b200-train", daemon=True)
+        t.start()
+        while t.is_alive():
+            t.join(self.heartbeat_every)
+            if t.is_alive():
+                self.connection.process_data_events(time_limit=0)
+                self.heartbeats_served += 1
+        if failure:
+            raise failure[0]
 
     def handle_batch(self, batch):
         """batch: list of (method, properties, body).  Replies and acks each job after the batch is trained

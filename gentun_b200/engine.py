@@ -21,6 +21,7 @@ METRICS = {"rmse": 0, "logloss": 1}
 MAX_BIN = 256
 MAX_NODES = 2047
 NUM_GENES = 11
+_DTYPES = {np.float32: 0, np.float64: 1, np.int64: 2}
 
 TREE_NODE = np.dtype([("feat", np.int32), ("bin", np.int32), ("value", np.float32), ("gain", np.float32)])
 NODE_ROWS = np.dtype([("begin", np.uint32), ("count", np.uint32), ("buf", np.int32), ("state", np.int32)])
@@ -55,7 +56,7 @@ class Stats(C.Structure):
 _lib = None
 _lib_lock = threading.Lock()
 
-EXPORTS = ("gt_engine_create", "gt_engine_prepare", "gt_engine_eval", "gt_engine_eval_ex", "gt_engine_destroy",
+EXPORTS = ("gt_engine_create", "gt_engine_create_from", "gt_engine_prepare", "gt_engine_eval", "gt_engine_eval_ex", "gt_engine_destroy",
            "gt_engine_fold_sizes", "gt_engine_get_fold_rows", "gt_engine_get_cuts", "gt_engine_get_bins",
            "gt_engine_get_stats", "gt_make_folds", "gt_last_error", "gt_version",
            "gt_column_cuts_noalloc", "gt_column_cuts_noalloc_max_rows")
@@ -74,6 +75,7 @@ def load_library():
         L = C.CDLL(LIB_PATH)
         vp, i32, i64 = C.c_void_p, C.c_int32, C.c_int64
         L.gt_engine_create.argtypes = [vp, i64, i32, i64, vp, C.POINTER(DataOpts), C.POINTER(vp)]
+        L.gt_engine_create_from.argtypes = [vp, i32, i64, i32, i64, i64, vp, i32, C.POINTER(DataOpts), C.POINTER(vp)]
         L.gt_engine_prepare.argtypes = [vp, i32]
         L.gt_engine_eval.argtypes = [vp, i32, vp, C.POINTER(FitOpts), vp, vp]
         L.gt_engine_eval_ex.argtypes = [vp, i32, vp, C.POINTER(FitOpts), vp, vp, C.POINTER(Dump)]
@@ -109,14 +111,38 @@ def make_folds(n, nfold, seed=0):
     return perm, fb
 
 
+# what xgboost uses for a parameter the caller leaves out (XgboostModel only dict.update()s the genes it is given into
+# its parameter dict, xgboost_models.py:16-22, so a genome that tunes two genes leaves the rest at these)
+XGB_DEFAULTS = {"eta": 0.3, "min_child_weight": 1.0, "max_depth": 6, "gamma": 0.0, "max_delta_step": 0.0, "subsample": 1.0,
+                "colsample_bytree": 1.0, "colsample_bylevel": 1.0, "lambda": 1.0, "alpha": 0.0, "scale_pos_weight": 1.0}
+# parameter names xgboost would honour but this engine does not implement: refusing beats silently ignoring them
+_UNSUPPORTED = {"tree_method", "max_bin", "grow_policy", "max_leaves", "colsample_bynode", "num_parallel_tree",
+                "monotone_constraints", "interaction_constraints", "base_score", "seed", "sampling_method",
+                "learning_rate", "min_split_loss", "reg_alpha", "reg_lambda"}
+_PASSIVE = {"booster", "objective", "eval_metric", "silent", "nthread", "n_jobs", "verbosity"}
+
+
+def complete_genes(genes):
+    """The 11 tuned parameters of one individual: absent ones take xgboost's defaults; a key that would change what
+    xgboost trains but that this engine cannot honour raises."""
+    bad = [k for k in genes if k in _UNSUPPORTED]
+    if bad:
+        raise NotImplementedError("gentun_b200 does not implement the xgboost parameter(s) %s" % sorted(bad))
+    unknown = [k for k in genes if k not in XGB_DEFAULTS and k not in _PASSIVE]
+    if unknown:
+        raise ValueError("unknown hyperparameter(s) %s" % sorted(unknown))
+    out = dict(XGB_DEFAULTS)
+    out.update({k: v for k, v in genes.items() if k in XGB_DEFAULTS})
+    return out
+
+
 def genes_matrix(genes_list):
-    """[n, 11] float64 in the genome order of XgboostIndividual; extra keys are ignored, like a dict.update."""
+    """[n, 11] float64 in the genome order of XgboostIndividual (absent genes at xgboost's defaults)."""
     out = np.empty((len(genes_list), NUM_GENES), dtype=np.float64)
     for i, g in enumerate(genes_list):
+        full = complete_genes(g)
         for j, name in enumerate(GENE_ORDER):
-            if name not in g:
-                raise ValueError("gene '%s' missing" % name)
-            out[i, j] = float(g[name])
+            out[i, j] = float(full[name])
     return out
 
 
@@ -150,14 +176,26 @@ class Engine(object):
             _check(self._lib.gt_engine_create(C.c_void_p(xp), self.n, self.f, int(ldx), C.c_void_p(yp), C.byref(opts),
                                               C.byref(self._h)))
         else:
-            xa = np.ascontiguousarray(np.asarray(x, dtype=np.float32))
-            ya = np.ascontiguousarray(np.asarray(y, dtype=np.float32).reshape(-1))
-            if xa.ndim != 2 or xa.shape[0] != ya.shape[0]:
+            # the arrays go to the library as they lie in memory (a float64 DataFrame is column-major): the cast to
+            # float32 that xgb.DMatrix applies and the row-major layout are made on the device
+            xa = np.asarray(x)
+            if xa.dtype not in (np.float32, np.float64):
+                xa = xa.astype(np.float64 if xa.dtype.kind in "iub" and xa.dtype.itemsize > 2 else np.float32)
+            if xa.ndim != 2:
+                raise ValueError("x must be [n, f] and y [n]")
+            if not (xa.flags.c_contiguous or xa.flags.f_contiguous):
+                xa = np.ascontiguousarray(xa)
+            ya = np.asarray(y).reshape(-1)
+            if ya.dtype not in (np.float32, np.float64, np.int64):
+                ya = ya.astype(np.float32)
+            ya = np.ascontiguousarray(ya)
+            if xa.shape[0] != ya.shape[0]:
                 raise ValueError("x must be [n, f] and y [n]")
             self.n, self.f = xa.shape
             self._keep = None
-            _check(self._lib.gt_engine_create(xa.ctypes.data, self.n, self.f, self.f, ya.ctypes.data, C.byref(opts),
-                                              C.byref(self._h)))
+            rs, cs = (self.f, 1) if xa.flags.c_contiguous else (1, self.n)
+            _check(self._lib.gt_engine_create_from(xa.ctypes.data, _DTYPES[xa.dtype.type], self.n, self.f, rs, cs,
+                                                   ya.ctypes.data, _DTYPES[ya.dtype.type], C.byref(opts), C.byref(self._h)))
         self.device = int(device)
 
     def close(self):
@@ -237,53 +275,79 @@ class Engine(object):
 
 
 # ---- engine cache: the GA re-creates Population objects every generation and every tournament
-# (gentun/algorithms.py:38-41, 51-55), so engines are keyed by the identity of the data objects.
+# (gentun/algorithms.py:38-41, 51-55), so engines live outside the populations, keyed by the identity of the data
+# objects.  An entry dies with its data (weakref.finalize), is rebuilt when the data were changed in place (a cheap
+# fingerprint is compared on every lookup), and takes its memoised fitness values with it: the memo is keyed by a
+# per-engine serial number that is never reused, not by an address.
 _engines = {}
 _memo = {}
+_serial = [0]
 
 
 def default_device():
     return int(os.environ.get("GENTUN_B200_DEVICE", os.environ.get("LOCAL_RANK", "0")))
 
 
+def _fingerprint(a):
+    """Shape, type, address and a strided sample of the values: enough to notice in-place rescaling or relabelling."""
+    v = np.asarray(a)
+    flat = v.reshape(-1) if v.flags.c_contiguous else v.T.reshape(-1) if v.flags.f_contiguous else v.ravel()
+    step = max(1, flat.shape[0] // 61)
+    sample = np.ascontiguousarray(flat[::step][:64])
+    return (v.shape, str(v.dtype), v.__array_interface__["data"][0], sample.tobytes(), flat[-1:].tobytes())
+
+
+def _drop(key):
+    hit = _engines.pop(key, None)
+    if hit is None:
+        return
+    eng = hit["engine"]
+    for k in [k for k in _memo if k[0] == eng.serial]:
+        del _memo[k]
+    eng.close()
+
+
 def engine_for(x, y, device=None):
     dev = default_device() if device is None else int(device)
-    key = (id(x), id(y), dev)
-    hit = _engines.get(key)
-    if hit is not None:
-        rx, ry, eng = hit
-        if rx() is x and ry() is y:
-            return eng
-        eng.close()
-        _engines.pop(key, None)
     if x is None or y is None:
         raise ValueError("x_train / y_train are required to evaluate fitness")
+    key = (id(x), id(y), dev)
+    fp = (_fingerprint(x), _fingerprint(y))
+    hit = _engines.get(key)
+    if hit is not None:
+        if hit["x"]() is x and hit["y"]() is y and hit["fp"] == fp:
+            return hit["engine"]
+        _drop(key)   # a recycled id, or data changed in place: the old engine and its memo entries are void
     eng = Engine(x, y, device=dev)
+    _serial[0] += 1
+    eng.serial = _serial[0]
 
     def _ref(o):
         try:
-            return weakref.ref(o)
+            r = weakref.ref(o)
+            weakref.finalize(o, _drop, key)   # the data died: free the device copy and the per-job buffers now
+            return r
         except TypeError:
             return lambda o=o: o
-    _engines[key] = (_ref(x), _ref(y), eng)
+    _engines[key] = {"x": _ref(x), "y": _ref(y), "fp": fp, "engine": eng}
     return eng
 
 
 def clear_engines():
-    for _, _, eng in list(_engines.values()):
-        eng.close()
-    _engines.clear()
+    for key in list(_engines):
+        _drop(key)
     _memo.clear()
 
 
 def memo_key(eng, genes, params):
-    return (id(eng), tuple(float(genes[k]) for k in GENE_ORDER), tuple(sorted(params.items())))
+    return (getattr(eng, "serial", -1), tuple(float(genes[k]) for k in GENE_ORDER), tuple(sorted(params.items())))
 
 
 def evaluate_many(x, y, genes_list, params, use_memo=True):
     """Fitness for many gene dicts sharing `params`; identical (genes, params) are trained once
     (xgb.cv is deterministic for fixed genes)."""
     eng = engine_for(x, y)
+    genes_list = [complete_genes(g) for g in genes_list]
     keys = [memo_key(eng, g, params) for g in genes_list]
     todo, todo_keys = [], []
     seen = set()

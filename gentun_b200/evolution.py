@@ -32,7 +32,7 @@ class GeneticAlgorithm(object):
 
     def _spawn_population(self, members):
         """A population of the same class around `members`.  The reference re-creates the population class with
-        exactly these arguments for every generation and every tournament, which is why engines and broker
+        exactly these arguments for every generation (and for every tournament), which is why engines and broker
         credentials are kept outside the instance."""
         source = self.population
         return self.get_population_type()(source.get_species(), self.x_train, self.y_train, individual_list=members,
@@ -45,8 +45,16 @@ class GeneticAlgorithm(object):
             self.generation += 1
 
     def tournament_select(self):
+        """Fittest of `tournament_size` members drawn without replacement (algorithms.py:50-56: same `random.sample`
+        call, same first-wins tie rule).  The reference wraps the contenders in a throw-away population, 2(P - 1) of them
+        per generation, only to call get_fittest on it; every member already has its fitness here (evolve_population
+        evaluated the generation in one batch), so the winner is picked directly.  Contenders without a fitness -- a
+        caller using this method on its own -- still go through a population, i.e. through the batch point."""
         size = self.population.get_size()
         contenders = [self.population[i] for i in random.sample(range(size), self.tournament_size)]
+        if all(ind.get_fitness_status() for ind in contenders):
+            pick = max if self.population.get_fitness_criteria() else min
+            return pick(contenders, key=lambda ind: ind.get_fitness())
         return self._spawn_population(contenders).get_fittest()
 
     def evolve_population(self):

@@ -49,34 +49,63 @@ def shard_plan(costs, world_size):
     return [np.asarray(p, dtype=np.int64) for p in picks]
 
 
+def _raise_for_bad(values, where):
+    bad = [i for i, v in enumerate(values) if not np.isfinite(v)]
+    if bad:
+        raise RuntimeError("gentun_b200: individual(s) %s produced a non-finite fitness (%s); the reference would hand "
+                           "nan/inf to max()/min(), whose result then depends on the order of the population" % (bad, where))
+
+
 def evaluate_sharded(engine, genes_list, params, local_eval=None):
-    """Fitness vector for genes_list, identical on every rank."""
+    """Fitness vector for genes_list, identical on every rank.  A rank whose evaluation fails still takes part in the
+    all-gather and reports the failure there, so every rank raises together instead of the others waiting for ever."""
     n = len(genes_list)
     if local_eval is None:
         def local_eval(sub):
             return engine.evaluate(sub, **params)[0]
     dist = _dist()
     if dist is None:
-        return np.asarray(local_eval(list(genes_list)), dtype=np.float64)
+        out = np.asarray(local_eval(list(genes_list)), dtype=np.float64)
+        _raise_for_bad(out, "single process")
+        return out
     import torch
     world, rank = dist.get_world_size(), dist.get_rank()
     plan = shard_plan([fit_cost(g) for g in genes_list], world)
     mine = plan[rank]
-    local = np.asarray(local_eval([genes_list[i] for i in mine]), dtype=np.float64) if len(mine) else np.zeros(0)
+    failure = None
+    local = np.zeros(0)
+    if len(mine):
+        try:
+            local = np.asarray(local_eval([genes_list[i] for i in mine]), dtype=np.float64)
+        except Exception as exc:   # reported to every rank below
+            failure = exc
+            local = np.zeros(len(mine))
     width = max(len(p) for p in plan)
     backend = dist.get_backend()
     dev = torch.device("cuda", torch.cuda.current_device()) if backend == "nccl" else torch.device("cpu")
-    send = torch.full((width,), float("nan"), dtype=torch.float64, device=dev)
+    # row 0: fitness values; row 1: 1.0 where row 0 holds a value this rank evaluated; last column of row 1: failure flag
+    send = torch.zeros((2, width + 1), dtype=torch.float64, device=dev)
     if len(mine):
-        send[:len(mine)] = torch.from_numpy(local).to(dev)
-    recv = torch.empty((world * width,), dtype=torch.float64, device=dev)
-    dist.all_gather_into_tensor(recv, send)
-    table = recv.cpu().numpy().reshape(world, width)
-    out = np.full(n, np.nan)
+        send[0, :len(mine)] = torch.from_numpy(local).to(dev)
+        send[1, :len(mine)] = 1.0
+    send[1, width] = 1.0 if failure is not None else 0.0
+    recv = torch.empty((world * 2 * (width + 1),), dtype=torch.float64, device=dev)
+    dist.all_gather_into_tensor(recv, send.reshape(-1))
+    table = recv.cpu().numpy().reshape(world, 2, width + 1)
+    failed = [r for r in range(world) if table[r, 1, width] != 0.0]
+    if failed:
+        if failure is not None:
+            raise failure
+        raise RuntimeError("gentun_b200: fitness evaluation failed on rank(s) %s" % failed)
+    out = np.empty(n)
+    done = np.zeros(n, dtype=bool)
     for r in range(world):
-        out[plan[r]] = table[r, :len(plan[r])]
-    if np.isnan(out).any():
-        raise RuntimeError("gentun_b200: fitness all-gather left %d individuals unevaluated" % int(np.isnan(out).sum()))
+        k = len(plan[r])
+        out[plan[r]] = table[r, 0, :k]
+        done[plan[r]] = table[r, 1, :k] == 1.0
+    if not done.all():
+        raise RuntimeError("gentun_b200: fitness all-gather left %d individuals unevaluated" % int((~done).sum()))
+    _raise_for_bad(out, "gathered from %d ranks" % world)
     return out
 
 

@@ -98,6 +98,19 @@ typedef struct {
 int gt_engine_create(const float* X, int64_t n, int32_t f, int64_t ldx, const float* y,
                      const gt_data_opts* opts, gt_engine** out);
 
+/* The same call for the arrays gentun's scripts really pass (tests/test_wine-quality.py:17-19 hands xgb.DMatrix a
+ * pandas DataFrame of float64, which is column-major in memory, and an int64 Series): host X in its own element
+ * type and layout, no host-side copy or cast by the caller.  Strides are in elements; either x_col_stride == 1
+ * (row-major, x_row_stride >= f) or x_row_stride == 1 (column-major, x_col_stride >= n).  The matrix is staged
+ * tile by tile through pinned buffers the library keeps, cast to float on the device (the cast DMatrix applies)
+ * and laid out row-major there.  y is cast on the host.  opts->x_on_device must be 0. */
+#define GT_DTYPE_F32 0
+#define GT_DTYPE_F64 1
+#define GT_DTYPE_I64 2   /* labels only */
+int gt_engine_create_from(const void* X, int32_t x_dtype, int64_t n, int32_t f, int64_t x_row_stride,
+                          int64_t x_col_stride, const void* y, int32_t y_dtype, const gt_data_opts* opts,
+                          gt_engine** out);
+
 /* Replaces what xgb.cv derives from (data, nfold) alone (training.py mknfold; per-slice quantile
  * sketch and GHistIndexMatrix built lazily by each Booster): folds, cut points, uint8 bin matrices.
  * Cached per nfold; gt_engine_eval calls it on demand. */

@@ -102,6 +102,41 @@ def test_worker_batches_jobs_and_handles_tuples(broker):
     assert i == 4 and ind.nfold == 2
 
 
+def test_worker_serves_heartbeats_while_a_batch_trains(broker):
+    """A long batch must not starve the connection: the worker keeps calling process_data_events while the engine
+    call runs (the reference's worker has a heartbeat thread, worker.py:26-33), and a failure in the training thread
+    surfaces on the worker's own thread."""
+    import time
+    import gentun_b200 as gentun
+
+    class Slow(XgboostIndividual):
+        @classmethod
+        def evaluate_batch(cls, individuals):
+            time.sleep(0.35)
+            for ind in individuals:
+                ind.set_fitness(stub_fitness(ind.get_genes()))
+
+    random.seed(9)
+    with contextlib.redirect_stdout(io.StringIO()):
+        pop = gentun.DistributedPopulation(Slow, size=3, rabbit_queue="q5")
+        worker = gentun.GentunWorker(Slow, "x", "y", rabbit_queue="q5", batch_size=3, batch_wait=0.2, heartbeat_every=0.05)
+        t = threading.Thread(target=lambda: worker.work(max_batches=1), daemon=True)
+        t.start()
+        pop.get_fittest()
+        t.join(timeout=10)
+    assert worker.heartbeats_served >= 3
+
+    class Broken(XgboostIndividual):
+        @classmethod
+        def evaluate_batch(cls, individuals):
+            raise RuntimeError("engine failed")
+
+    with contextlib.redirect_stdout(io.StringIO()):
+        w2 = gentun.GentunWorker(Broken, "x", "y", rabbit_queue="q6", batch_size=2, batch_wait=0.1, heartbeat_every=0.05)
+        with pytest.raises(RuntimeError, match="engine failed"):
+            w2._evaluate([Broken(None, None)])
+
+
 def test_distributed_grid_population(broker):
     import gentun_b200 as gentun
     random.seed(8)

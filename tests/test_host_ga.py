@@ -65,6 +65,29 @@ def test_random_population_and_ga_minimize():
     assert random.random() == GOLD["draw_after_ga_minimize"]
 
 
+def test_tournaments_build_no_throwaway_populations():
+    """the reference constructs a population per tournament, 2(P - 1) per generation
+    (algorithms.py:50-56); here one generation constructs exactly one (the next generation), with the same offspring."""
+    built = []
+
+    class Counting(gentun.Population):
+        def __init__(self, *a, **kw):
+            built.append(1)
+            super(Counting, self).__init__(*a, **kw)
+
+    random.seed(SEED)
+    pop = Counting(StubIndividual, None, None, size=24, additional_parameters={"nfold": 3}, maximize=False)
+    del built[:]
+    gens = run_ga(pop, 4)
+    assert len(built) == 4
+    check_gens(gens, GOLD["ga_minimize"])
+    # a contender whose fitness is unknown still reaches the batch point through a population
+    ga = gentun.GeneticAlgorithm(Counting(StubIndividual, None, None, size=8, maximize=False), tournament_size=8)
+    del built[:]
+    winner = ga.tournament_select()
+    assert len(built) == 1 and winner.get_fitness() == min(ga.population[i].get_fitness() for i in range(8))
+
+
 def test_ga_maximize_without_elitism():
     random.seed(SEED + 1)
     pop = gentun.Population(StubIndividual, None, None, size=16, maximize=True)
@@ -168,6 +191,61 @@ def test_batch_hook_groups_and_memo(monkeypatch):
     model = gentun.XgboostModel(x, y, pop[1].get_genes(), nfold=3)
     assert model.cross_validate() == pop[1].get_fitness() and len(calls) == 1   # memo hit
     eng_mod._memo.clear()
+
+
+def test_engine_cache_follows_the_data(monkeypatch):
+    """Engines and memoised fitness are tied to the data: a new dataset never sees another dataset's values (not even
+    at a recycled address), data changed in place gets a new engine, and an engine is closed when its data die."""
+    import gc
+    import numpy as np
+    from gentun_b200 import engine as eng_mod
+    made, closed = [], []
+
+    class FakeEngine(object):
+        def __init__(self, x, y, device=0):
+            self.tag = float(np.asarray(x)[0, 0])
+            made.append(self.tag)
+
+        def evaluate(self, genes_list, **params):
+            return np.array([self.tag + g["eta"] for g in genes_list]), None
+
+        def close(self):
+            closed.append(self.tag)
+
+    monkeypatch.setattr(eng_mod, "Engine", FakeEngine)
+    eng_mod.clear_engines()
+    g = dict(eng_mod.XGB_DEFAULTS)
+    params = {"nfold": 3}
+    x1, y1 = np.full((8, 2), 1.0), np.zeros(8)
+    assert eng_mod.evaluate_many(x1, y1, [g], params) == [1.3]
+    assert eng_mod.evaluate_many(x1, y1, [g], params) == [1.3] and made == [1.0]      # memo + cached engine
+    x1[:] = 5.0                                                                          # rescaled in place
+    assert eng_mod.evaluate_many(x1, y1, [g], params) == [5.3] and made == [1.0, 5.0] and closed == [1.0]
+    del x1
+    gc.collect()
+    assert closed == [1.0, 5.0] and not eng_mod._engines and not eng_mod._memo         # data died: engine and memo gone
+    for v in (7.0, 9.0):                                                                 # datasets in a loop, ids may recycle
+        xv = np.full((8, 2), v)
+        assert eng_mod.evaluate_many(xv, y1, [g], params) == [v + 0.3]
+        del xv
+        gc.collect()
+    assert closed == [1.0, 5.0, 7.0, 9.0]
+    eng_mod.clear_engines()
+
+
+def test_partial_genomes_take_xgboost_defaults():
+    """A genome that tunes two genes trains with xgboost's defaults for the rest (XgboostModel dict.update()s only what
+    it is given, xgboost_models.py:16-22); a parameter this engine cannot honour is refused, not ignored."""
+    from gentun_b200.engine import genes_matrix, GENE_ORDER
+    m = genes_matrix([{"eta": 0.1, "max_depth": 4, "booster": "gbtree", "silent": 1}])
+    want = dict(eta=0.1, min_child_weight=1, max_depth=4, gamma=0, max_delta_step=0, subsample=1, colsample_bytree=1,
+                colsample_bylevel=1, alpha=0, scale_pos_weight=1)
+    want["lambda"] = 1
+    assert [m[0, j] for j in range(11)] == [float(want[k]) for k in GENE_ORDER]
+    with pytest.raises(NotImplementedError):
+        genes_matrix([{"eta": 0.1, "tree_method": "exact"}])
+    with pytest.raises(ValueError):
+        genes_matrix([{"eta": 0.1, "not_a_parameter": 3}])
 
 
 def test_unsupported_parameters_raise():

@@ -54,6 +54,45 @@ def test_two_rank_allgather_reassembles_the_population():
     assert sorted(o["mine"] for o in outs) == [5, 6]      # every individual trained on exactly one rank
 
 
+FAILING_WORKER = WORKER.replace(
+    'return np.array([g["max_depth"] * 10 + g["eta"] for g in sub])',
+    'if dist.get_rank() == 1: raise ValueError("boom on rank 1")\n    return np.array([g["max_depth"] * 10 + g["eta"] for g in sub])'
+).replace('out = sharding.evaluate_sharded(None, genes, {}, local_eval=local_eval)',
+          'try:\n    out = sharding.evaluate_sharded(None, genes, {}, local_eval=local_eval)\n'
+          'except Exception as exc:\n    print(json.dumps({"rank": dist.get_rank(), "error": type(exc).__name__ + ": " + str(exc)}))\n'
+          '    dist.destroy_process_group()\n    sys.exit(0)')
+
+
+def test_a_failing_rank_makes_every_rank_raise():
+    """One rank's evaluation throws: the others must not wait in the all-gather for ever; all of them raise."""
+    import json
+    port = str(free_port())
+    procs = []
+    for rank in range(2):
+        env = dict(os.environ, RANK=str(rank), WORLD_SIZE="2", PORT=port, MASTER_ADDR="127.0.0.1")
+        procs.append(subprocess.Popen([sys.executable, "-c", FAILING_WORKER], env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True))
+    errs = {}
+    for p in procs:
+        so, se = p.communicate(timeout=180)
+        assert p.returncode == 0, se[-2000:]
+        o = json.loads(so.strip().splitlines()[-1])
+        errs[o["rank"]] = o.get("error")
+    assert errs[1] == "ValueError: boom on rank 1"
+    assert errs[0] is not None and "rank(s) [1]" in errs[0]
+
+
+def test_non_finite_fitness_raises_after_the_batch():
+    from gentun_b200 import sharding
+    import pytest
+
+    class Eng(object):
+        def evaluate(self, genes, **params):
+            return np.array([1.0, float("nan"), 3.0]), None
+
+    with pytest.raises(RuntimeError, match=r"individual\(s\) \[1\]"):
+        sharding.evaluate_sharded(Eng(), [{"max_depth": 3}] * 3, {})
+
+
 def test_shard_plan_balances_depths():
     from gentun_b200.sharding import shard_plan
     depths = [10, 3, 10, 4, 9, 3, 8, 5]
