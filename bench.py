@@ -1,14 +1,15 @@
 #!/usr/bin/env python
-"""bench.py -- CV fits/sec of the fitness-evaluation hot path on BASELINE.json's headline shape.
+"""bench.py -- CV fits/sec of the fitness-evaluation hot path on BASELINE.json's shapes.
 
-A step = one batch of individuals (consecutive members of the seeded 256-individual population of
-config C3: synthetic 1M x 50 regressor, nfold=5, 100 boosting rounds) evaluated by ONE call of the
-C ABI (gt_engine_eval).  `value` times that call with the binned folds already resident in HBM;
-`e2e` times gt_engine_create (host X, y -> device, sketch, binning) + gt_engine_eval + fitness
-read-back, i.e. everything xgb.DMatrix + xgb.cv do per fit in the reference.
+A step = one batch of individuals (members of the seeded population of the chosen config) evaluated by ONE call of
+the C ABI (gt_engine_eval).  `value` times that call with the binned folds already resident in HBM; `e2e` times the
+call a gentun user makes -- Population(XgboostIndividual, x, y, ...).get_fittest() on a float64 pandas DataFrame --
+from host arrays to the fittest individual: ingestion (H2D + cast), folds, quantile sketch, binning, training and
+the fitness read-back, i.e. everything xgb.DMatrix + xgb.cv do per fit in the reference.
 
-    python bench.py --gpus N --steps K --warmup W            # our arm
-    python bench.py --impl reference --gpus N --steps K ...   # CPU restatement of the reference path
+    python bench.py --gpus N --steps K --warmup W                    # our arm, headline config C3
+    python bench.py --workload c1|c2|c4|c5 ...                        # the other named shapes of BASELINE.json
+    python bench.py --impl reference --gpus N --steps K --warmup W    # CPU restatement of the reference path
 """
 import argparse
 import json
@@ -25,10 +26,28 @@ sys.path.insert(0, ROOT)
 
 METRIC = "cv_fits_per_sec"
 UNIT = "fits/s"
+WINE = os.path.join(ROOT, "tests", "data", "winequality-white.csv")
+# nfold / rounds / early stopping are what the config passes through additional_parameters; `ips` is the
+# number of individuals one GPU evaluates per step
 WORKLOADS = {
-    # name: (rows, features, nfold, rounds, population, classification, seed)
-    "c3": (1_000_000, 50, 5, 100, 256, False, 1003),
-    "c3-small": (100_000, 50, 5, 20, 256, False, 1003),   # for quick checks only, never a bench line
+    "c1": dict(data="wine", population=100, grid=False, nfold=3, rounds=5000, esr=100, ips=100, cls=False,
+               text="C1 of BASELINE.json: XgboostIndividual regressor on winequality-white.csv (4898x11), Population size=100, "
+                    "nfold=3, up to 5000 rounds with early stopping 100, one generation per step"),
+    "c2": dict(data="wine", population=200, grid=True, nfold=3, rounds=5000, esr=100, ips=200, cls=False,
+               text="C2 of BASELINE.json: GridPopulation eta x max_depth x colsample_bytree (5x8x5 = 200 individuals) on "
+                    "winequality-white.csv, nfold=3, up to 5000 rounds with early stopping 100, the whole grid per step"),
+    "c3": dict(data="synthetic", rows=1_000_000, features=50, seed=1003, population=256, nfold=5, rounds=100, esr=100, ips=32,
+               cls=False, text="C3 of BASELINE.json: XgboostIndividual regressor, synthetic 1000000x50, Population size=256, "
+                               "nfold=5, 100 boosting rounds"),
+    "c4": dict(data="synthetic", rows=10_000_000, features=100, seed=1004, population=128, nfold=3, rounds=100, esr=100, ips=16,
+               cls=True, text="C4 of BASELINE.json: binary:logistic / logloss, synthetic 10000000x100, Population size=128, "
+                              "nfold=3, 100 boosting rounds, max_depth up to 10"),
+    "c5": dict(data="synthetic", rows=4_000_000, features=200, seed=1005, population=1024, nfold=5, rounds=100, esr=100, ips=32,
+               cls=False, text="C5 of BASELINE.json: regressor, synthetic 4000000x200, Population size=1024, nfold=5, "
+                               "100 boosting rounds, population sharded over the GPUs with a fitness all-gather"),
+    # quick checks only, never a bench line
+    "c3-small": dict(data="synthetic", rows=100_000, features=50, seed=1003, population=256, nfold=5, rounds=20, esr=100, ips=32,
+                     cls=False, text="c3-small (quick check, not a bench line)"),
 }
 
 
@@ -39,28 +58,79 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
-    ap.add_argument("--inds-per-step", type=int, default=32,
-                    help="individuals per step per GPU (32 = one GPU's share of the 256-individual generation on 8 GPUs)")
+    ap.add_argument("--inds-per-step", type=int, default=0, help="individuals per step per GPU (default: the workload's)")
     ap.add_argument("--e2e-steps", type=int, default=2)
-    ap.add_argument("--cpu-rounds", type=int, default=2, help="boosting rounds in the CPU sample")
+    ap.add_argument("--cpu-sample-rounds", type=int, default=10, help="boosting rounds of the bounded cpu_baseline sample in our arm")
+    ap.add_argument("--cpu-budget-s", type=float, default=900.0,
+                    help="reference arm: full fits are timed until this much wall clock is used; later steps are sampled")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--rounds", type=int, default=0, help="override boosting rounds (profiling only; not a bench line)")
     return ap.parse_args()
 
 
-def describe(wl, args, world):
-    n, f, nfold, rounds, pop, cls, seed = WORKLOADS[wl]
+def load_workload(name, rounds_override=0):
+    """(x32, y, x_api, y_api, genes, params, spec): x32/y feed the C ABI directly, x_api/y_api are what a gentun script
+    holds (a float64 DataFrame and a Series), genes is the seeded population."""
+    import pandas as pd
+    from tests.synth import make_dataset, seeded_population_genes
+    spec = dict(WORKLOADS[name])
+    if rounds_override:
+        spec["rounds"] = rounds_override
+        spec["text"] += " [rounds overridden to %d: profiling run, not a bench line]" % rounds_override
+    if spec["data"] == "wine":
+        df = pd.read_csv(WINE, delimiter=";")
+        y_api, x_api = df["quality"], df.drop(["quality"], axis=1)     # tests/test_wine-quality.py:17-19
+        x32 = np.ascontiguousarray(x_api.values, dtype=np.float32)
+        y = np.ascontiguousarray(y_api.values, dtype=np.float32)
+        spec["rows"], spec["features"] = x32.shape
+        if spec["grid"]:
+            genes = grid_genes()
+        else:
+            genes = seeded_population_genes(spec["population"])
+    else:
+        x32, y = make_dataset(spec["rows"], spec["features"], spec["seed"], classification=spec["cls"])
+        x_api = pd.DataFrame(np.asfortranarray(x32, dtype=np.float64))   # column-major float64, like read_csv gives
+        y_api = pd.Series(y.astype(np.float64))
+        genes = seeded_population_genes(spec["population"])
+    params = dict(nfold=spec["nfold"], num_boost_round=spec["rounds"], early_stopping_rounds=spec["esr"])
+    if spec["cls"]:
+        params.update(objective="binary:logistic", eval_metric="logloss")
+    return x32, y, x_api, y_api, genes, params, spec
+
+
+def grid_genes():
+    """The 200 gene sets of tests/test_grid_wine-quality.py:20-30, built by GridPopulation itself."""
+    import contextlib
+    import io
+    import random
+    from gentun_b200 import GridPopulation, XgboostIndividual
+    grid = {'eta': [0.001, 0.005, 0.01, 0.015, 0.2], 'max_depth': range(3, 11),
+            'colsample_bytree': [0.80, 0.85, 0.90, 0.95, 1.0]}
+    state = random.getstate()
+    random.seed(20240601)
+    with contextlib.redirect_stdout(io.StringIO()):
+        pop = GridPopulation(XgboostIndividual, None, None, genes_grid=grid, additional_parameters={'nfold': 3}, maximize=False)
+    random.setstate(state)
+    return [dict(pop[i].get_genes()) for i in range(pop.get_size())]
+
+
+def fits_l2(spec):
+    return spec["nfold"] * spec["rows"] * ((spec["features"] + 31) // 32 * 32) <= (126 << 20)
+
+
+def describe(spec, ips, world):
+    n, f, nfold = spec["rows"], spec["features"], spec["nfold"]
+    shards = max(1, spec["population"] // ips)
     return {
-        "workload": "C3 of BASELINE.json: XgboostIndividual regressor, synthetic %dx%d, Population size=%d, nfold=%d, "
-                    "%d boosting rounds" % (n, f, pop, nfold, rounds) if wl == "c3" else wl,
-        "rows": n, "features": f, "nfold": nfold, "num_boost_round": rounds, "population": pop,
-        "individuals_per_step_per_gpu": args.inds_per_step,
-        "step": "the population seeded with random.seed(20240601) is dealt once into %d cost-balanced shards of %d "
-                "individuals (gentun_b200.sharding.shard_plan); in step s rank r runs ONE gt_engine_eval on shard "
-                "(s*n_gpus + r) mod %d, so per-GPU work is the same at every n_gpus and 8 GPUs evaluate one whole "
-                "generation per step" % (pop // args.inds_per_step, args.inds_per_step, pop // args.inds_per_step),
-        "l2": "inputs exceed L2: binned folds %d MB + per-job state > 126 MB" % (nfold * n * ((f + 31) // 32 * 32) >> 20),
-        "parallelism": "population sharded over %d GPU(s), fitness all-gather" % world,
+        "workload": spec["text"], "rows": n, "features": f, "nfold": nfold, "num_boost_round": spec["rounds"],
+        "early_stopping_rounds": spec["esr"], "population": spec["population"], "individuals_per_step_per_gpu": ips,
+        "step": "the population seeded with random.seed(20240601) is dealt once into %d cost-balanced shard(s) of %d individuals "
+                "(gentun_b200.sharding.shard_plan); in step s rank r runs ONE gt_engine_eval on shard (s*n_gpus + r) mod %d, so "
+                "per-GPU work is the same at every n_gpus" % (shards, ips, shards),
+        "l2": ("inputs exceed L2: binned folds %d MB + per-job state" % (nfold * n * ((f + 31) // 32 * 32) >> 20)) if not fits_l2(spec)
+              else "inputs fit L2 (%d KB of bins per fold): 256 MB written between timed steps to flush it" % (n * ((f + 31) // 32 * 32) >> 10),
+        "parallelism": "population sharded over %d GPU(s), fitness all-gather" % world if spec["data"] != "wine"
+                       else "%d replica(s) of the same generation (a 36 KB bin matrix gives 8 GPUs nothing to share out)" % world,
     }
 
 
@@ -159,62 +229,77 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def ncu_traffic():
-    """dram bytes per histogram launch from the committed ncu capture, if one exists."""
+def ncu_traffic(workload):
+    """DRAM bytes per histogram launch from the committed ncu capture of this workload, with the algorithmic bytes of
+    the SAME launches beside it (profiles/hist_traffic.json), or (None, None)."""
     path = os.path.join(ROOT, "profiles", "hist_traffic.json")
     if os.path.exists(path):
         try:
-            return json.load(open(path)).get("dram_bytes_per_launch")
+            d = json.load(open(path))
+            if d.get("workload", "c3") == workload.split("-")[0]:
+                return d.get("dram_bytes_per_launch"), d.get("algorithmic_bytes_per_launch")
         except Exception:
-            return None
-    return None
+            pass
+    return None, None
 
 
-def cpu_sample(x, y, genes, nfold, rounds_total, rounds_sample, nthread=0):
-    """Bounded sample of the reference's per-fit CPU path with the oracle port: the full per-fit set-up
-    (fold slices, quantile sketch, binning: what xgb.DMatrix + the lazy Booster init redo for every
-    individual) plus `rounds_sample` boosting rounds over all folds, extrapolated linearly to
-    rounds_total.  Returns (seconds per fit, detail)."""
+def cpu_fit(x, y, genes, params, nthread, rounds_sample=None):
+    """The reference's per-fit CPU path with the oracle port: the full per-fit set-up (fold slices, quantile sketch,
+    binning: what xgb.DMatrix + the lazy Booster init redo for every individual) plus the boosting rounds -- all of them,
+    or `rounds_sample` of them extrapolated linearly.  Returns (seconds per fit, detail)."""
     from oracle import orc
+    rounds_total = params["num_boost_round"]
+    run = rounds_total if not rounds_sample else min(rounds_sample, rounds_total)
+    opts = dict(params, num_boost_round=run, nthread=nthread)
+    if run < rounds_total:
+        opts["early_stopping_rounds"] = 0
     t0 = time.perf_counter()
-    ctx = orc.Context(x, y, nfold, nthread=nthread)
+    ctx = orc.Context(x, y, params["nfold"], nthread=nthread)
     t_setup = time.perf_counter() - t0
     t0 = time.perf_counter()
-    ctx.cv(genes, orc.make_opts(nfold=nfold, num_boost_round=rounds_sample, early_stopping_rounds=100, nthread=nthread))
+    res = ctx.cv(genes, orc.make_opts(**opts))
     t_rounds = time.perf_counter() - t0
     ctx.close()
-    return t_setup + t_rounds * (rounds_total / float(rounds_sample)), {"setup_s": t_setup, "rounds_s": t_rounds}
+    full = run == rounds_total
+    sec = t_setup + (t_rounds if full else t_rounds * (rounds_total / float(run)))
+    return sec, {"setup_s": t_setup, "rounds_s": t_rounds, "rounds_run": res["rounds"], "full": full, "fitness": res["fitness"]}
 
 
 def run_reference(args):
+    """The reference's own CPU path for the same config: one individual's complete fit (set-up + every boosting round,
+    early stopping as configured) per step, on all host cores.  The thread count is passed explicitly so that a
+    launcher's OMP_NUM_THREADS=1 cannot shrink it, and `cores` is what OpenMP really used."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
     from oracle import orc
-    from tests.synth import make_dataset, seeded_population_genes
-    n, f, nfold, rounds, pop, cls, seed = WORKLOADS[args.workload]
-    x, y = make_dataset(n, f, seed, classification=cls)
-    genes = seeded_population_genes(pop)
-    cores = orc.max_threads()
-    times = []
-    for s in range(args.warmup + args.steps):
-        if s >= 1 and s < args.warmup:
-            continue   # one warm-up sample is enough for a CPU loop; keeps the run within minutes
-        sec, _ = cpu_sample(x, y, genes[s % pop], nfold, rounds, args.cpu_rounds)
-        if s >= args.warmup:
-            times.append(sec)
+    x, y, _, _, genes, params, spec = load_workload(args.workload, args.rounds)
+    nthread = orc.host_cores()
+    cores = orc.threads_in_use(nthread)
+    ips = args.inds_per_step or spec["ips"]
+    times, fulls, t_start = [], 0, time.perf_counter()
+    n_steps = 1 + args.steps if args.warmup else args.steps      # one warm-up fit is enough for a CPU loop
+    for s in range(n_steps):
+        over = (time.perf_counter() - t_start) > args.cpu_budget_s
+        sample = max(2, params["num_boost_round"] // 20) if over else None
+        sec, detail = cpu_fit(x, y, genes[s % len(genes)], params, nthread, rounds_sample=sample)
+        if args.warmup and s == 0:
+            continue
+        times.append(sec)
+        fulls += 1 if detail["full"] else 0
     sec_per_fit = float(np.mean(times))
     value = 1.0 / sec_per_fit
-    sample = ("oracle port of the reference's per-fit path (no xgboost on this box): per individual, full set-up "
-              "(fold slices + quantile sketch + binning of %dx%d x %d folds) + %d of %d boosting rounds x %d folds, "
-              "extrapolated linearly to %d rounds; %d individuals of the seeded population"
-              % (n, f, nfold, args.cpu_rounds, rounds, nfold, rounds, len(times)))
+    sample = ("oracle port of the reference's per-fit path (no xgboost on this box): per individual, full set-up (fold slices + "
+              "quantile sketch + binning of %dx%d x %d folds) + ALL boosting rounds (early stopping as configured), %d threads; "
+              "%d individuals of the seeded population, %d timed in full, %d sampled and extrapolated after the %.0f s budget"
+              % (spec["rows"], spec["features"], spec["nfold"], cores, len(times), fulls, len(times) - fulls, args.cpu_budget_s))
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": sec_per_fit * 1e3, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f64 accumulators over f32 gradients", "data": "synthetic",
-        "config": describe(args.workload, args, 1),
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "vs_baseline": None, "dtype": "f64 accumulators over f32 gradients", "data": "synthetic" if spec["data"] == "synthetic" else "winequality-white.csv",
+        "config": describe(spec, ips, 1),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
+                         "extrapolated_fraction": 1.0 - fulls / float(len(times))},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     emit(line)
@@ -241,16 +326,13 @@ def emit(line):
 def main():
     args = parse_args()
     quiet_stdout()
-    if args.rounds:
-        wl = list(WORKLOADS[args.workload]); wl[3] = args.rounds
-        WORKLOADS[args.workload + "-profile"] = tuple(wl)
-        args.workload = args.workload + "-profile"
     if args.impl == "reference":
         return run_reference(args)
     import torch
     import torch.distributed as dist
+    import gentun_b200 as gentun
     from gentun_b200.engine import Engine, genes_matrix
-    from tests.synth import make_dataset, seeded_population_genes
+    from gentun_b200.sharding import fit_cost, shard_plan
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -267,29 +349,35 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    n, f, nfold, rounds, pop, cls, seed = WORKLOADS[args.workload]
-    x, y = make_dataset(n, f, seed, classification=cls)
-    genes = seeded_population_genes(pop)
-    params = dict(nfold=nfold, num_boost_round=rounds, early_stopping_rounds=100)
-    ips = args.inds_per_step
-
-    from gentun_b200.sharding import fit_cost, shard_plan
+    x, y, x_api, y_api, genes, params, spec = load_workload(args.workload, args.rounds)
+    pop = len(genes)
+    ips = args.inds_per_step or spec["ips"]
     if pop % ips:
         raise SystemExit("--inds-per-step must divide the population size %d" % pop)
     shards = shard_plan([fit_cost(g) for g in genes], pop // ips)
+    replicas = spec["data"] == "wine"     # a 36 KB bin matrix: every GPU evaluates the same generation
 
-    def step_genes(s):
-        """This rank's share of step s: one of the population's cost-balanced shards (the same dealing
+    def step_genes(s, r=None):
+        """Rank r's share of step s: one of the population's cost-balanced shards (the same dealing
         gentun_b200.sharding does for a generation on pop // ips GPUs), so every rank always has one shard's work."""
-        return [genes[i] for i in shards[(s * world + rank) % len(shards)]]
+        r = rank if r is None else r
+        return [genes[i] for i in shards[(s * (1 if replicas else world) + (0 if replicas else r)) % len(shards)]]
+
+    small = fits_l2(spec)
+    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device="cuda") if small else None
+
+    def flush_l2():
+        if flush_buf is not None:
+            flush_buf.fill_(1)
 
     # ---- resident arm: binned folds in HBM before the timed region
     eng = Engine(x, y, device=local_rank, collect_timing=True)
-    eng.prepare(nfold)
+    eng.prepare(spec["nfold"])
     prep_ms = eng.stats()["prepare_ms"]
     gather_buf = torch.empty(world * ips, dtype=torch.float64, device="cuda") if world > 1 else None
 
     def one_step(s):
+        flush_l2()
         fit, _ = eng.evaluate(step_genes(s), **params)
         if world > 1:   # the path's one collective: fitness scalars back to every rank
             dist.all_gather_into_tensor(gather_buf, torch.from_numpy(fit).cuda())
@@ -320,48 +408,55 @@ def main():
     if world > 1:
         dist.all_reduce(rank_ms)
     value = world * ips * args.steps / (wall_ms_max / 1e3)
-
-    # ---- end-to-end arm: host buffers in, fitness out, through the C ABI; includes H2D of X and y,
-    # fold construction, quantile sketch and binning (what the reference redoes per fit)
     eng.close()
-    # the end-to-end arm reads its inputs from pinned host memory, as a caller that cares about H2D speed would
-    xp = torch.from_numpy(x).pin_memory().numpy()
-    yp = torch.from_numpy(y).pin_memory().numpy()
+    del eng
+
+    # ---- end-to-end arm: the call a gentun user makes.  A float64 DataFrame and a Series go into a Population, and
+    # get_fittest() returns the fittest individual: ingestion (pinned-tile H2D + cast on the device), folds, sketch,
+    # binning, training and the fitness read-back are all inside the timed region.  Under torchrun every rank holds the
+    # same population of world * ips individuals and gentun_b200.sharding deals it over the ranks (fitness all-gather).
     e2e_ms = 0.0
-    gm_bytes = 0
     for s in range(args.e2e_steps + 1 if args.e2e_steps else 0):
+        gs = []
+        for r in range(1 if replicas else world):
+            gs += step_genes(args.warmup + args.steps + s, r)
+        flush_l2()
         barrier()
         t1 = time.perf_counter()
-        e2 = Engine(xp, yp, device=local_rank)
-        gs = step_genes(args.warmup + args.steps + s)
-        fit, _ = e2.evaluate(gs, **params)
-        if world > 1:
-            dist.all_gather_into_tensor(gather_buf, torch.from_numpy(fit).cuda())
-        e2.close()
+        gentun.clear_engines()          # a new dataset object every time a user script starts: nothing is cached
+        inds = [gentun.XgboostIndividual(x_api, y_api, genes=dict(g), **params) for g in gs]
+        best = gentun.Population(gentun.XgboostIndividual, x_api, y_api, individual_list=inds, maximize=False).get_fittest()
+        assert np.isfinite(best.get_fitness())
         barrier()
         if s > 0:   # first pass is a warm-up
             e2e_ms += (time.perf_counter() - t1) * 1e3
-        gm_bytes = genes_matrix(gs).nbytes
+    gentun.clear_engines()
     te = torch.tensor([e2e_ms], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
-    e2e_value = world * ips * args.e2e_steps / (float(te[0]) / 1e3) if args.e2e_steps else None
-    h2d = x.nbytes + y.nbytes + gm_bytes
-    d2h = ips * 12 + nfold * f * 4 + y.nbytes * 0
+    n_e2e = ips * (1 if replicas else world)   # wine: the one generation, dealt over the ranks by the product itself
+    e2e_value = n_e2e * args.e2e_steps / (float(te[0]) / 1e3) if args.e2e_steps else None
+    x_bytes = int(np.asarray(x_api).nbytes + np.asarray(y_api).nbytes)
+    h2d = x_bytes + genes_matrix(step_genes(0)).nbytes
+    d2h = ips * 12 + spec["nfold"] * spec["features"] * 4
 
     if rank == 0:
         peak, peak_src = measured_peak()
         achieved = hist_bytes / (hist_ms * 1e-3) / 1e9 if hist_ms > 0 else None
+        traffic, traffic_alg = ncu_traffic(args.workload)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": wall_ms_max / args.steps, "device_ms_per_step": dev_ms_max / args.steps,
             "device_ms_per_step_by_rank": [round(v, 1) for v in rank_ms.tolist()],
+            "s_per_generation": spec["population"] / value if value else None,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "int64 fixed-point histograms over f32 gradients (f64 split gains)", "data": "synthetic",
-            "config": describe(args.workload, args, world),
+            "dtype": "int32/int64 fixed-point histograms over f32 gradients (f64 split gains)",
+            "data": "synthetic" if spec["data"] == "synthetic" else "winequality-white.csv",
+            "config": describe(spec, ips, world),
             "roofline": {
                 "bound": "hbm", "kernel": "k_hist", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": (achieved / peak) if achieved else None, "traffic": ncu_traffic(), "peak_source": peak_src,
+                "frac": (achieved / peak) if achieved else None, "traffic": traffic,
+                "traffic_algorithmic_bytes_same_launches": traffic_alg, "peak_source": peak_src,
                 "frac_of_8tbs_spec": (achieved / 8000.0) if achieved else None,
                 "launches": hist_launches, "avg_launch_ms": hist_ms / max(hist_launches, 1),
                 "algorithmic_bytes_per_launch": hist_bytes / max(hist_launches, 1),
@@ -369,17 +464,21 @@ def main():
                 "share_of_step": hist_ms / dev_ms if dev_ms > 0 else None,
             },
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "includes": "gt_engine_create (H2D of X,y + folds + sketch + binning) + gt_engine_eval + destroy"},
+                    "includes": "Population(XgboostIndividual, float64 DataFrame, Series, individual_list).get_fittest(): ingestion "
+                                "(pinned-tile H2D + cast), folds, sketch, binning, gt_engine_eval, fitness read-back, engine teardown"},
             "gpu_launches": int(launches), "prepare_ms": prep_ms, "clocks": clocks,
         }
         if not args.no_cpu_baseline and world == 1:
             from oracle import orc
-            sec, detail = cpu_sample(x, y, genes[0], nfold, rounds, args.cpu_rounds)
+            nthread = orc.host_cores()
+            wine = spec["data"] == "wine"
+            sec, detail = cpu_fit(x, y, genes[0], params, nthread, rounds_sample=None if wine else args.cpu_sample_rounds)
             line["cpu_baseline"] = {
-                "value": 1.0 / sec, "unit": UNIT, "cores": orc.max_threads(), "kind": "port",
-                "sample": "oracle port (no xgboost on this box): individual 0 of the seeded population, full per-fit "
-                          "set-up (folds + sketch + binning, %.1f s) + %d of %d rounds x %d folds (%.1f s), extrapolated "
-                          "linearly to %d rounds" % (detail["setup_s"], args.cpu_rounds, rounds, nfold, detail["rounds_s"], rounds)}
+                "value": 1.0 / sec, "unit": UNIT, "cores": orc.threads_in_use(nthread), "kind": "port",
+                "sample": "oracle port (no xgboost on this box): individual 0 of the seeded population, full per-fit set-up (folds + "
+                          "sketch + binning, %.1f s) + %d of %d rounds x %d folds (%.1f s)%s; the full-length measurement is "
+                          "`bench.py --impl reference`" % (detail["setup_s"], detail["rounds_run"], params["num_boost_round"], spec["nfold"],
+                                                          detail["rounds_s"], "" if detail["full"] else ", extrapolated linearly")}
         emit(line)
     if world > 1:
         dist.destroy_process_group()

@@ -561,7 +561,9 @@ const uint8_t* orc_ctx_bins_col(const orc_ctx* c, int k) { return c->bins_col[k]
 const int64_t* orc_ctx_perm(const orc_ctx* c) { return c->perm; }
 
 /* ------------------------------------------------------------------------------------------ */
-/* Tree dump record, heap indexed (node i -> children 2i+1, 2i+2). feat: -2 absent, -1 leaf, >=0 split */
+/* Tree dump record, heap indexed (node i -> children 2i+1, 2i+2). feat: -2 absent, -1 leaf, >=0 split.
+ * value: leaf value of a leaf; for a split node the loss_chg of the best OTHER candidate (0 if none).
+ * gain: loss_chg of the best candidate -- also for a node that was evaluated and stayed a leaf (0 if never evaluated). */
 typedef struct { int32_t feat; int32_t bin; float value; float gain; } orc_node_dump;
 #define ORC_MAX_NODES 2047
 
@@ -569,7 +571,7 @@ typedef struct {
   double G, H; float root_gain, weight;
   int64_t begin, count;    /* segment in the row-set array */
   int32_t state;           /* 0 absent, 1 open, 2 split, 3 leaf */
-  int32_t feat, bin; float loss_chg; double GL, HL;
+  int32_t feat, bin; float loss_chg, second_chg; double GL, HL;
 } orc_node;
 
 typedef struct { double g, h; } orc_gh;
@@ -688,7 +690,7 @@ static void orc_grow_tree(const orc_ctx* c, int k, const orc_params* p, int roun
   int* build_ids = (int*)malloc(sizeof(int) * 1024);
   /* root */
   orc_node* root = &nodes[0];
-  root->state = 1; root->begin = 0; root->count = ntr;
+  root->state = 1; root->begin = 0; root->count = ntr; root->loss_chg = 0.0f; root->second_chg = 0.0f;
   {
     build_ids[0] = 0;
     double t0 = orc_now();
@@ -720,6 +722,7 @@ static void orc_grow_tree(const orc_ctx* c, int k, const orc_params* p, int roun
       any_open |= 1;
       const orc_gh* Hn = hist_of_node[nid];
       float best_chg = 0.0f; int best_f = -1, best_b = -1; double best_GL = 0, best_HL = 0;
+      float second_chg = 0.0f;   /* best loss_chg among the OTHER candidates (test diagnostics only: how close the decision was) */
       for (int j = 0; j < f; ++j) {
         if (!level_mask[j]) continue;
         const orc_gh* hj = Hn + (size_t)j * ORC_MAX_BIN;
@@ -730,7 +733,8 @@ static void orc_grow_tree(const orc_ctx* c, int k, const orc_params* p, int roun
           if (HL >= p->min_child_weight && HR >= p->min_child_weight) {
             float chg = calc_split_gain(p, GL, HL, GR, HR) - nd->root_gain;
             /* SplitEntry::NeedReplace: features ascend, so strictly greater wins; inf is rejected */
-            if (!isinf(chg) && chg > best_chg) { best_chg = chg; best_f = j; best_b = b; best_GL = GL; best_HL = HL; }
+            if (!isinf(chg) && chg > best_chg) { second_chg = best_chg; best_chg = chg; best_f = j; best_b = b; best_GL = GL; best_HL = HL; }
+            else if (!isinf(chg) && chg > second_chg) second_chg = chg;
           }
         }
       }
@@ -741,7 +745,7 @@ static void orc_grow_tree(const orc_ctx* c, int k, const orc_params* p, int roun
         if (best_HL == 0 || HR == 0) valid = 0;
         if (best_chg < p->gamma) valid = 0;
       }
-      nd->loss_chg = best_chg;
+      nd->loss_chg = best_chg; nd->second_chg = second_chg;
       if (!valid) { nd->state = 3; continue; }
       nd->state = 2; nd->feat = best_f; nd->bin = best_b; nd->GL = best_GL; nd->HL = best_HL;
     }
@@ -787,6 +791,7 @@ static void orc_grow_tree(const orc_ctx* c, int k, const orc_params* p, int roun
       L->weight = calc_weight(p, L->G, L->H); R->weight = calc_weight(p, R->G, R->H);
       L->root_gain = calc_gain(p, L->G, L->H); R->root_gain = calc_gain(p, R->G, R->H);
       L->state = R->state = children_evaluated ? 1 : 3;
+      L->loss_chg = R->loss_chg = 0.0f; L->second_chg = R->second_chg = 0.0f;
       L->begin = nd->begin; L->count = nl; R->begin = nd->begin + nl; R->count = nd->count - nl;
       ti = tj;
     }
@@ -927,8 +932,9 @@ int orc_cv(const orc_ctx* c, const double* genes, const orc_opts* o, orc_result*
       if (trees && it < trees_rounds) {
         orc_node_dump* td = trees + ((size_t)k * (size_t)trees_rounds + (size_t)it) * ORC_MAX_NODES;
         for (int i = 0; i < ORC_MAX_NODES; ++i) {
-          if (nodes[i].state == 2) { td[i].feat = nodes[i].feat; td[i].bin = nodes[i].bin; td[i].value = 0; td[i].gain = nodes[i].loss_chg; }
-          else if (nodes[i].state == 3) { td[i].feat = -1; td[i].bin = 0; td[i].value = leaf_of_node[i]; td[i].gain = 0; }
+          /* split nodes carry the runner-up candidate's loss_chg in `value` (the engine's dump has 0 there) */
+          if (nodes[i].state == 2) { td[i].feat = nodes[i].feat; td[i].bin = nodes[i].bin; td[i].value = nodes[i].second_chg; td[i].gain = nodes[i].loss_chg; }
+          else if (nodes[i].state == 3) { td[i].feat = -1; td[i].bin = 0; td[i].value = leaf_of_node[i]; td[i].gain = nodes[i].loss_chg; }
           else { td[i].feat = -2; td[i].bin = 0; td[i].value = 0; td[i].gain = 0; }
         }
         if (final_rows && it == trees_rounds - 1) memcpy(final_rows + (size_t)k * (size_t)final_rows_stride, rows_a, sizeof(int64_t) * (size_t)ntr);

@@ -56,6 +56,71 @@ def _properties(n, f, nfold, classification, rounds=4, n_ind=3):
     eng.close()
 
 
+def test_c3_shape_parity_with_oracle():
+    """The benchmark's own shape (1M x 50, nfold 5) against the oracle: cut points and bin indices bit-exact on every
+    fold, per-round CV means within 1e-4 relative (north_star's fitness tolerance) for the deepest individual of the
+    seeded population, one with max_delta_step != 0 and alpha != 0, and one with sampling genes, and tree identity
+    graded node by node (tests/treediff.py)."""
+    from gentun_b200.engine import Engine
+    from oracle import orc
+    from tests.treediff import grade, root_causes
+    n, f, nfold, R = 1_000_000, 50, 5, 5
+    x, y = make_dataset(n, f, seed=1003)
+    eng = Engine(x, y)
+    ctx = orc.Context(x, y, nfold, nthread=orc.host_cores())
+    for k in range(nfold):
+        cu, nc = eng.cuts(nfold, k)
+        ocu, onc = ctx.cuts(k)
+        assert np.array_equal(nc, onc)
+        for j in range(f):
+            assert np.array_equal(cu[j, :nc[j]].view(np.uint32), ocu[j, :nc[j]].view(np.uint32)), (k, j)
+        if k in (0, nfold - 1):
+            ntr = ctx.ntrain(k)
+            assert np.array_equal(eng.bins(nfold, k)[:ntr], ctx.train_bins(k))     # oracle's own C binning of the train slice
+    pop = seeded_population_genes(256)
+    deep = next(g for g in pop if g["max_depth"] == 10 and g["subsample"] == 1.0 and g["colsample_bytree"] == 1.0 and g["colsample_bylevel"] == 1.0)
+    reg = next(g for g in pop if g["max_delta_step"] != 0 and g["alpha"] != 0 and g["subsample"] == 1.0
+               and g["colsample_bytree"] == 1.0 and g["colsample_bylevel"] == 1.0 and g is not deep)
+    samp = next(g for g in pop if g["subsample"] < 1.0 and g["colsample_bytree"] < 1.0)
+    gs = [deep, reg, samp]
+    fit, rounds, extra = eng.evaluate(gs, trace=True, tree_rounds=R, nfold=nfold, num_boost_round=R)
+    compared, causes = 0, []
+    for i, g in enumerate(gs):
+        want = ctx.cv(g, orc.make_opts(nfold=nfold, num_boost_round=R, nthread=orc.host_cores()), trace=True, trees_rounds=R)
+        np.testing.assert_allclose(extra["trace"][i, :R], want["trace"], rtol=1e-4)       # north_star: 1e-4 relative
+        assert abs(fit[i] - want["fitness"]) <= 1e-4 * abs(want["fitness"])
+        for k in range(nfold):
+            n_cmp, c = root_causes(extra["trees"][i, k], want["trees"][k], g["gamma"])
+            compared += n_cmp
+            causes += c
+    ties, flips, wrong = grade(causes)
+    print("tree identity at 1M x 50: %d nodes compared, %d root-cause mismatches (%d fp32 ties, %d quantisation flips)"
+          % (compared, len(causes), ties, flips))
+    assert not wrong, wrong
+    assert len(causes) <= 0.01 * compared, (len(causes), compared)
+    eng.close()
+    ctx.close()
+
+
+def test_hundred_round_drift_against_frozen_oracle():
+    """Full-length fits (100 rounds) against oracle traces frozen by tests/golden/make_drift_golden.py: the benchmark
+    shape under squared error, and a logistic fit with min_child_weight near the deep nodes' hessian sums.  Every round's
+    CV mean stays within north_star's 1e-4 relative; the recorded drift is quoted in DESIGN.md."""
+    import json
+    import os
+    from gentun_b200.engine import Engine
+    gold = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "drift_100_rounds.json")))
+    for name, c in gold.items():
+        x, y = make_dataset(c["shape"][0], c["shape"][1], c["data_seed"], classification=c["classification"])
+        eng = Engine(x, y)
+        fit, rounds, extra = eng.evaluate([c["genes"]], trace=True, **c["params"])
+        eng.close()
+        want = np.asarray(c["oracle_trace"])
+        got = extra["trace"][0, :len(want)]
+        np.testing.assert_allclose(got, want, rtol=1e-4, err_msg=name)      # north_star: 1e-4 relative, every round
+        assert rounds[0] == len(want)
+
+
 def test_c3_shape_1m_by_50_regression():
     _properties(1_000_000, 50, 5, False)
 

@@ -10,6 +10,7 @@ import pytest
 
 from oracle import orc
 from tests.synth import make_dataset
+from tests.treediff import grade, root_causes
 
 pytestmark = pytest.mark.gpu
 
@@ -168,16 +169,16 @@ def test_tree_structure_and_row_partitions(wine_pair):
     gs = [genes(max_depth=5), genes(max_depth=8, min_child_weight=0, eta=0.1)]
     R = 4
     fit, rounds, extra = eng.evaluate(gs, tree_rounds=R, rows_round=R - 1, nfold=3, num_boost_round=R)
-    same = total = 0
+    compared, causes = 0, []
     for i, g in enumerate(gs):
         want = ctx.cv(g, orc.make_opts(nfold=3, num_boost_round=R), trees_rounds=R)
         for k in range(3):
             bins = ctx.train_bins(k)
+            n_cmp, c = root_causes(extra["trees"][i, k], want["trees"][k], g["gamma"])
+            compared += n_cmp
+            causes += c
             for r in range(R):
                 mine, ref = extra["trees"][i, k, r], want["trees"][k, r]
-                exists = ref["feat"] != -2
-                total += int(exists.sum())
-                same += int(((mine["feat"] == ref["feat"]) & (mine["bin"] == ref["bin"]))[exists].sum())
                 # round 0 starts from identical gradients: structure must be identical
                 if r == 0:
                     assert np.array_equal(mine["feat"], ref["feat"]) and np.array_equal(mine["bin"], ref["bin"])
@@ -219,7 +220,14 @@ def test_tree_structure_and_row_partitions(wine_pair):
                 assert np.array_equal(seg.astype(np.int64), rows), (i, k, nid)
                 checked += 1
             assert checked >= 3
-    assert same / total > 0.98, (same, total)
+    # Trees may differ from the oracle's only where the oracle's own decision was a near-tie: within a few fp32 ulps of
+    # the gain (allowed by north_star) or within the 2^-19 quantisation of the gradients (DESIGN.md quotes the measured
+    # rate).  A root-cause mismatch with a wider margin would be a wrong split.
+    ties, flips, wrong = grade(causes)
+    print("tree identity on wine: %d nodes compared, %d root-cause mismatches (%d fp32 ties, %d quantisation flips)"
+          % (compared, len(causes), ties, flips))
+    assert not wrong, wrong
+    assert len(causes) <= 0.01 * compared, (len(causes), compared)
 
 
 def test_early_stopping_matches(wine_pair):

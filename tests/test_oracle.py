@@ -170,6 +170,134 @@ def test_one_round_of_stumps_matches_hand_computation():
     ctx.close()
 
 
+# ---- a second, structurally different restatement (recursive, float64, no histograms, no subtraction trick) for the
+# parts of SURVEY.md A.5-A.9 that the stump test does not reach: several levels, alpha (ThresholdL1), max_delta_step
+# (clamped weight and the matching gain), gamma as a pre-stop, min_child_weight on both sides, scale_pos_weight, the
+# logistic objective and metric, base-score estimation, and several rounds of prediction updates.
+def _sigmoid32(m):
+    m = np.asarray(m, dtype=np.float32)
+    return (np.float32(1.0) / (np.exp(np.minimum(-m, np.float32(88.7))) + np.float32(1.0) + np.float32(1e-16))).astype(np.float32)
+
+
+def _grad(obj, margin, y, spw):
+    w = np.where(y == np.float32(1.0), np.float32(spw), np.float32(1.0)).astype(np.float32)
+    if obj == "binary:logistic":
+        p = _sigmoid32(margin)
+        return ((p - y) * w).astype(np.float32), (np.maximum(p * (np.float32(1.0) - p), np.float32(1e-16)) * w).astype(np.float32)
+    return ((margin - y) * w).astype(np.float32), (np.ones_like(y) * w).astype(np.float32)
+
+
+def _tl1(G, a):
+    return G - a if G > a else G + a if G < -a else 0.0
+
+
+def _weight(G, H, p):
+    if H < p["min_child_weight"] or H <= 0:
+        return 0.0
+    w = -_tl1(G, p["alpha"]) / (H + p["lambda"])
+    if p["max_delta_step"] != 0 and abs(w) > p["max_delta_step"]:
+        w = np.copysign(p["max_delta_step"], w)
+    return float(np.float32(w))
+
+
+def _gain(G, H, p):
+    if H <= 0:
+        return 0.0
+    if p["max_delta_step"] == 0:
+        return _tl1(G, p["alpha"]) ** 2 / (H + p["lambda"])
+    w = _weight(G, H, p)
+    return -(2.0 * G * w + (H + p["lambda"]) * w * w)
+
+
+def _grow(xs, g, h, rows, depth, p, out, path=()):
+    """Returns nothing; fills `out` with (path -> leaf weight) and (path -> (feature, threshold)) entries."""
+    G, H = float(g[rows].sum()), float(h[rows].sum())
+    best = (0.0, None)
+    if depth < p["max_depth"]:
+        root = _gain(G, H, p)
+        for j in range(xs.shape[1]):
+            col = xs[rows, j]
+            for thr in np.unique(col)[1:]:
+                left = col < thr
+                GL, HL = float(g[rows][left].sum()), float(h[rows][left].sum())
+                if HL < p["min_child_weight"] or H - HL < p["min_child_weight"]:
+                    continue
+                chg = np.float32(np.float32(_gain(GL, HL, p)) + np.float32(_gain(G - GL, H - HL, p))) - np.float32(root)
+                if chg > best[0]:
+                    best = (float(chg), (j, thr))
+    if best[1] is None or best[0] <= 1e-6 or best[0] < p["gamma"]:
+        out[path] = _weight(G, H, p)
+        return
+    j, thr = best[1]
+    out[path] = (j, thr)
+    left = xs[rows, j] < thr
+    _grow(xs, g, h, rows[left], depth + 1, p, out, path + (0,))
+    _grow(xs, g, h, rows[~left], depth + 1, p, out, path + (1,))
+
+
+def _apply(tree, xrow):
+    path = ()
+    while isinstance(tree[path], tuple):
+        j, thr = tree[path]
+        path += (0,) if xrow[j] < thr else (1,)
+    return tree[path]
+
+
+def _cv_by_hand(x, y, nfold, rounds, obj, metric, p):
+    np.random.seed(0)
+    chunks = np.array_split(np.random.permutation(len(y)), nfold)
+    trace = np.zeros(rounds)
+    for k in range(nfold):
+        te = chunks[k]
+        tr = np.concatenate([chunks[i] for i in range(nfold) if i != k])
+        g0, h0 = _grad(obj, np.zeros(len(tr), dtype=np.float32), y[tr], p["scale_pos_weight"])
+        stump = np.float32(-float(g0.astype(np.float64).sum()) / max(float(h0.astype(np.float64).sum()), 1e-6))
+        base = np.float32(-np.log(np.float32(1.0) / _sigmoid32(stump) - np.float32(1.0))) if obj == "binary:logistic" else stump
+        mtr = np.full(len(tr), base, dtype=np.float32)
+        mte = np.full(len(te), base, dtype=np.float32)
+        for r in range(rounds):
+            g, h = _grad(obj, mtr, y[tr], p["scale_pos_weight"])
+            tree = {}
+            _grow(x[tr], g.astype(np.float64), h.astype(np.float64), np.arange(len(tr)), 0, p, tree)
+            eta = np.float32(p["eta"])
+            mtr = (mtr + np.array([eta * np.float32(_apply(tree, row)) for row in x[tr]], dtype=np.float32)).astype(np.float32)
+            mte = (mte + np.array([eta * np.float32(_apply(tree, row)) for row in x[te]], dtype=np.float32)).astype(np.float32)
+            if metric == "logloss":
+                pr = _sigmoid32(mte).astype(np.float64)
+                pr = np.clip(pr, 1e-16, 1 - 1e-16)
+                e = -(y[te] * np.log(pr) + (1 - y[te]) * np.log(1 - pr))
+                trace[r] += e.mean() / nfold
+            else:
+                d = (y[te] - mte).astype(np.float64)
+                trace[r] += np.sqrt((d * d).mean()) / nfold
+    return trace
+
+
+@pytest.mark.parametrize("obj,metric,over", [
+    ("reg:linear", "rmse", dict(max_depth=3, alpha=2.0, min_child_weight=12)),
+    ("reg:linear", "rmse", dict(max_depth=3, max_delta_step=1, alpha=0.5, eta=0.7)),
+    ("reg:linear", "rmse", dict(max_depth=4, gamma=6.0, **{"lambda": 0.5})),
+    ("binary:logistic", "logloss", dict(max_depth=3, scale_pos_weight=2.5, min_child_weight=3)),
+    ("binary:logistic", "logloss", dict(max_depth=2, max_delta_step=2, eta=1.0, scale_pos_weight=0.5)),
+])
+def test_multilevel_growth_matches_recursive_restatement(obj, metric, over):
+    rng = np.random.default_rng(11)
+    n = 360
+    x = rng.integers(0, 7, size=(n, 4)).astype(np.float32)
+    score = x[:, 0] - 0.8 * x[:, 1] + 1.5 * (x[:, 2] > 3) + rng.standard_normal(n) * 0.7
+    if obj == "binary:logistic":
+        y = (score > np.median(score)).astype(np.float32)
+    else:
+        y = score.astype(np.float32)
+    g = genes(**over)
+    rounds = 3
+    ctx = orc.Context(x, y, 3)
+    got = ctx.cv(g, orc.make_opts(objective=obj, eval_metric=metric, nfold=3, num_boost_round=rounds, early_stopping_rounds=0), trace=True)
+    ctx.close()
+    want = _cv_by_hand(x, y, 3, rounds, obj, metric, g)
+    np.testing.assert_allclose(got["trace"], want, rtol=1e-6)
+
+
 def test_training_reduces_validation_error(wine_ctx, wine):
     r = wine_ctx.cv(genes(eta=0.1), orc.make_opts(nfold=3, num_boost_round=30), trace=True)
     assert r["trace"][-1] < r["trace"][0] < float(np.std(wine[1].values)) * 1.01
