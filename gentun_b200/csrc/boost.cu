@@ -87,6 +87,9 @@ __device__ void prepare_next_round(const Wave& w, int j) {
   r.G = 0; r.H = 0; r.begin = 0; r.cnt = (uint32_t)w.folds[jp.fold].ntrain;
   r.leaf = 0.f; r.root_gain = 0.f; r.loss_chg = 0.f; r.feat = -1; r.bin = 0; r.state = kOpen; r.buf = 0;
   r.narrow = r.cnt <= (uint32_t)kNarrowRows; r.absG = 0ull;
+#ifdef GT_DBG_NO_NARROW
+  r.narrow = 0;
+#endif
   TreeNode& t = w.tree[(size_t)j * kNodeCap];
   t.leaf = 0.f; t.feat = -1; t.bin = 0; t.state = kOpen;
 }
@@ -287,6 +290,7 @@ __global__ void __launch_bounds__(256) k_plan_hist(Wave w, int level) {
   __syncthreads();
   if (threadIdx.x == 255) {
     js.n_hist_items = min(s_scan[0][255], w.hist_cap);
+    if (s_scan[0][255] > hist_items_bound(w, level)) w.counters[7] = 1ull;   // items the grid would not reach
     js.n_pairs = s_scan[1][255];
     js.n_zero = min(s_scan[2][255], w.hist_cap);
     if (s_rows) atomicAdd(&w.counters[0], s_rows);
@@ -303,6 +307,9 @@ __device__ __forceinline__ HistEntry* node_hist(const Wave& w, const JobParams& 
 // exactly when the node gets its rows (Node::absG: k_hist for the root and every built child, parent - built for a
 // sibling); without that, rows * 2^19 bounds it.  Only nodes built by one CTA qualify (plain stores).  Else int64 pairs.
 __device__ __forceinline__ bool child_narrow(const Node& parent, uint32_t cnt, long long H) {
+#ifdef GT_DBG_NO_NARROW
+  return false;
+#endif
   if (cnt <= (uint32_t)kNarrowRows) return true;
   return cnt <= (uint32_t)kHistRows && parent.absG <= 0x7fffffffull && H <= 0x7fffffffll;
 }
@@ -326,6 +333,17 @@ __global__ void __launch_bounds__(256) k_hist_zero(Wave w, int level) {
     for (int i = threadIdx.x; i < cells; i += blockDim.x) h[i] = make_longlong2(0, 0);
   }
 }
+
+#ifdef GT_DBG_CLEAR_HIST   // debugging aid: every histogram slot of the level starts as zeros, so a read of a slot that
+                           // nothing wrote this level shows up as a changed result instead of depending on stale bytes
+__global__ void __launch_bounds__(256) k_dbg_clear_level(Wave w, int level) {
+  const int j = blockIdx.y;
+  const JobParams jp = w.jp[j];
+  if (level >= jp.max_depth) return;
+  longlong2* h = reinterpret_cast<longlong2*>(node_hist(w, jp, level, level_first(level) + blockIdx.x));
+  for (int i = threadIdx.x; i < w.groups * kBins * kLanes; i += blockDim.x) h[i] = make_longlong2(0x0123456789abcdefll, 0x0fedcba987654321ll);
+}
+#endif
 
 // ------------------------------------------------------------------ X5: histogram
 // One CTA = (job, work item, feature group of 32).  A warp takes 16 rows per step: lane = (row, 16-byte
@@ -809,7 +827,11 @@ __device__ __forceinline__ void settle_node(const JobParams& jp, int level, Node
   // Driver::IsChildValid; in addition a child whose hessian sum is below 2 * min_child_weight has no valid
   // candidate (both sides need H >= min_child_weight), so evaluating it could only make it a leaf: settle that now
   // and spare its histogram, scan and partition
+#ifdef GT_DBG_NO_EARLY_LEAF
+  const bool can_split = true;
+#else
   const bool can_split = hmin_q <= 0 || chq >= 2 * hmin_q;
+#endif
   const uint8_t child_state = (level + 1 < jp.max_depth && can_split) ? kOpen : kLeaf;
   Node& chn = nodes[2 * node + 1 + sd];
   const double g = (double)cgq * inv_sg, h = (double)chq * inv_sh;
@@ -1228,7 +1250,10 @@ __global__ void __launch_bounds__(256) k_plan_part(Wave w, int level) {
       items[ni] = PartItem{nid[s2], nd.begin + b, cnt, first_item, chunks[s2], nd.begin, nd.cnt, (int)nd.buf};
     }
   }
-  if (threadIdx.x == 255) js.n_part_items = min(s_scan[255], w.part_cap);
+  if (threadIdx.x == 255) {
+    js.n_part_items = min(s_scan[255], w.part_cap);
+    if (s_scan[255] > part_items_bound(w, level)) w.counters[7] = 2ull;
+  }
 }
 
 // The split feature's bin of a row comes from the feature-major copy of the bin matrix: rows of a node
@@ -1768,7 +1793,12 @@ void launch_grad(const Wave& w, cudaStream_t s) {
 }
 // Per-level launches cover only the jobs whose trees reach that level (a prefix of the depth-ordered job array).
 void launch_plan_hist(const Wave& w, int level, cudaStream_t s) { k_plan_hist<<<w.lvl_jobs[level], 256, 0, s>>>(w, level); }
-void launch_hist_zero(const Wave& w, int level, cudaStream_t s) { k_hist_zero<<<dim3(32, w.lvl_jobs[level]), 256, 0, s>>>(w, level); }
+void launch_hist_zero(const Wave& w, int level, cudaStream_t s) {
+#ifdef GT_DBG_CLEAR_HIST
+  k_dbg_clear_level<<<dim3(1 << level, w.lvl_jobs[level]), 256, 0, s>>>(w, level);
+#endif
+  k_hist_zero<<<dim3(32, w.lvl_jobs[level]), 256, 0, s>>>(w, level);
+}
 int launch_hist(const Wave& w, int level, cudaStream_t s) {   // returns the number of kernels launched
   int cap = hist_items_bound(w, level);
   if (w.groups % 2 == 0) k_hist<4><<<dim3(w.lvl_jobs[level] * (w.groups / 2), cap), 512, 2 * kHistSmem, s>>>(w, level);

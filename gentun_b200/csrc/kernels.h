@@ -46,13 +46,16 @@ void launch_round_end(const Wave& w, int first, double* fitness_out, int* rounds
 void launch_dump_trees(const Wave& w, int round, int tree_rounds, gt_tree_node* out, cudaStream_t s);
 void launch_dump_node_rows(const Wave& w, gt_node_rows* out, cudaStream_t s);
 
-// host-known upper bounds of the per-job work-item counts (grids are sized from these)
-inline int hist_items_bound(const Wave& w, int level) {
+// host-known upper bounds of the per-job work-item counts (grids are sized from these; the planners check them on the
+// device and raise the wave's error flag if a count ever exceeds its bound).  A level builds one child per split
+// parent -- usually the smaller one, but the LARGER one when its sibling was settled as a leaf at once -- so the rows
+// built in a level can approach all nt rows: sum of ceil(cnt / kHistRows) <= nt / kHistRows + number of parents.
+__host__ __device__ inline int hist_items_bound(const Wave& w, int level) {
   long long nt = w.nt_stride;
-  long long b = level == 0 ? (nt + kHistRows - 1) / kHistRows : nt / (2 * kHistRows) + (1ll << (level - 1)) + 1;
+  long long b = level == 0 ? (nt + kHistRows - 1) / kHistRows : nt / kHistRows + (1ll << (level - 1)) + 1;
   return (int)(b < w.hist_cap ? b : w.hist_cap);
 }
-inline int part_items_bound(const Wave& w, int level) {
+__host__ __device__ inline int part_items_bound(const Wave& w, int level) {
   long long b = (w.nt_stride + kPartRows - 1) / kPartRows + (1ll << level);
   return (int)(b < w.part_cap ? b : w.part_cap);
 }
