@@ -7,5 +7,5 @@ OUT="${GT_OUT:-$HERE/../libgentun_b200.so}"
 NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
 "$NVCC" -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -fmad=false \
   -ccbin /usr/bin/g++ -Xcompiler -fPIC -Xcompiler -O2 -shared ${GT_PTXAS_V:+-Xptxas -v} ${GT_DEFS} \
-  -o "$OUT" "$HERE/sketch.cu" "$HERE/boost.cu" "$HERE/engine.cu" 2>&1
+  -o "$OUT" "$HERE/sketch.cu" "$HERE/boost.cu" "$HERE/small.cu" "$HERE/engine.cu" 2>&1
 echo "built $OUT"

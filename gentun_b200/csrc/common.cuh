@@ -24,6 +24,9 @@ constexpr int kQuantBitsH = 17;     // hessians are near-constant (1 for squared
 constexpr int kPredRows = 2048;     // rows per predict CTA
 constexpr int kMaskWords = 8;       // feature masks: up to 256 features
 constexpr int kMaxWaveInds = 4096;  // individuals per wave (k_predict keeps their job list in shared memory)
+constexpr int kSmallThreads = 512;   // the shared-memory-resident regime (small.cu): threads per job
+constexpr int kSmallMaxTrain = 4095; // train rows per fold it takes: 4095 * 2^19 < 2^31 keeps every prefix sum in int32, 8 list elements per thread
+constexpr int kSmallMaxRows = 8192;  // rows (train + test) it takes: predictions live in shared memory
 
 enum NodeState : uint8_t { kAbsent = 0, kOpen = 1, kSplit = 2, kLeaf = 3 };
 
@@ -125,6 +128,27 @@ struct Wave {            // passed by value to kernels
   double* mpart;         // [n_jobs][pred_chunks] per-CTA metric partial sums
   double* trace;         // [n_inds][num_boost_round] or null
   unsigned long long* counters;  // [0] rows through hist, [1] node histograms built, [2] active individuals, [5 + level parity] pairs of the level, [7] work-list overflow (an error)
+};
+
+struct SmallWave {       // arguments of the shared-memory-resident kernel (small.cu), passed by value
+  int n_inds, nfold;
+  int n, f, fpad, nt_stride;
+  int objective, metric, num_boost_round, early_stopping_rounds;
+  const FoldDev* folds;
+  const uint32_t* base_lists;   // [nfold][f][nt_stride] (bin << 16 | row) of the train slice, sorted by bin, ties by row
+  const JobParams* jp;          // [n_inds][nfold]
+  const IndState* is;           // [n_inds] (out_index)
+  Node* nodes;                  // [ctas][kNodeCap]
+  TreeNode* tree;               // [ctas][kNodeCap]
+  uint32_t* lists;              // [ctas][2][f][nt_stride] ping-pong copies of the per-feature lists
+  double* fold_s;               // [teams][2][nfold] per-round metric sums of a team's folds
+  unsigned* team_bar;           // [teams] barrier counters (zeroed before the launch)
+  int* team_ind;                // [teams][2]
+  int* queue;                   // [1] next position in `order` (zeroed before the launch)
+  const int* order;             // [n_inds] individuals, most expensive first
+  double* trace;                // [n_inds][num_boost_round] or null
+  double* fitness_out;
+  int* rounds_out;
 };
 
 // counter-based generator (definition shared with the oracle by specification)

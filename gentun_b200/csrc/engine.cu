@@ -8,6 +8,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <memory>
@@ -117,6 +118,9 @@ struct FoldSet {
   std::vector<double> sum_not1_sq, sum_not1_lg;   // sum over labels != 1 of (0 - y) / (0.5 - y)
   std::vector<int64_t> n1, nnot1;
   double prepare_ms = 0;
+  // the shared-memory-resident regime (small.cu): per fold and feature, the train slice's rows sorted by bin
+  bool small_ok = false;
+  DevBuf<uint32_t> d_small_lists;             // [nfold][f][nt_stride] (bin << 16 | row)
 };
 
 // device buffers of gt_engine_eval, kept between calls (cudaMalloc / cudaFree of several GB per call
@@ -128,6 +132,12 @@ struct EvalBuffers {
   DevBuf<gt::PairRec> d_pairs; DevBuf<gt::PartItem> d_pitems; DevBuf<int> d_pleft; DevBuf<uint32_t> d_pflags;
   DevBuf<double> d_mpart; DevBuf<double> d_trace; DevBuf<unsigned long long> d_counters;
   DevBuf<double> d_fit; DevBuf<int> d_rounds; DevBuf<gt_tree_node> d_trees; DevBuf<gt_node_rows> d_nrows;
+};
+
+struct SmallBuffers {
+  DevBuf<gt::JobParams> d_jp; DevBuf<gt::IndState> d_is; DevBuf<gt::Node> d_nodes; DevBuf<gt::TreeNode> d_tree;
+  DevBuf<uint32_t> d_lists; DevBuf<double> d_fold_s; DevBuf<unsigned> d_bar; DevBuf<int> d_team_ind; DevBuf<int> d_queue;
+  DevBuf<int> d_order; DevBuf<double> d_trace; DevBuf<double> d_fit; DevBuf<int> d_rounds;
 };
 
 }  // namespace
@@ -145,6 +155,8 @@ struct gt_engine {
   int collect_timing = 0;
   std::map<int, std::unique_ptr<FoldSet>> foldsets;
   EvalBuffers bufs;
+  SmallBuffers small;
+  int force_streaming = 0;   // never take the shared-memory-resident path (tests compare the two regimes)
   gt_stats stats{};
 };
 
@@ -276,6 +288,35 @@ int prepare_impl(gt_engine* e, int nfold, FoldSet** out) {
   GT_CUDA(cudaMemcpyAsync(fs->d_grp_maxnc.p, h_maxnc.data(), sizeof(int) * h_maxnc.size(), cudaMemcpyHostToDevice, e->stream));
   GT_CUDA(fs->d_folds.ensure(nfold));
   GT_CUDA(cudaMemcpyAsync(fs->d_folds.p, h_folds.data(), sizeof(gt::FoldDev) * nfold, cudaMemcpyHostToDevice, e->stream));
+  {
+    int64_t ntmax = 0;
+    for (int k = 0; k < nfold; ++k) ntmax = std::max(ntmax, fs->ntrain[k]);
+    if (ntmax <= gt::kSmallMaxTrain && n <= gt::kSmallMaxRows) {
+      // small data: every feature's train rows sorted by bin (ties by row), the order small.cu keeps per node
+      const int64_t nt_stride = (ntmax + 31) / 32 * 32;
+      std::vector<uint8_t> h_bins((size_t)n * e->fpad);
+      std::vector<uint32_t> h_lists((size_t)nfold * f * nt_stride, 0u);
+      for (int k = 0; k < nfold; ++k) {
+        GT_CUDA(cudaMemcpyAsync(h_bins.data(), fs->d_bins[k].p, h_bins.size(), cudaMemcpyDeviceToHost, e->stream));
+        GT_CUDA(cudaStreamSynchronize(e->stream));
+        const int64_t ntr = fs->ntrain[k];
+        for (int j = 0; j < f; ++j) {
+          uint32_t* out = h_lists.data() + ((size_t)k * f + j) * nt_stride;
+          int64_t count[257] = {0};
+          for (int64_t r = 0; r < ntr; ++r) ++count[h_bins[(size_t)r * e->fpad + j] + 1];
+          for (int b = 0; b < 256; ++b) count[b + 1] += count[b];
+          for (int64_t r = 0; r < ntr; ++r) {
+            const uint32_t b = h_bins[(size_t)r * e->fpad + j];
+            out[count[b]++] = (b << 16) | (uint32_t)r;
+          }
+        }
+      }
+      GT_CUDA(fs->d_small_lists.ensure(h_lists.size()));
+      GT_CUDA(cudaMemcpyAsync(fs->d_small_lists.p, h_lists.data(), sizeof(uint32_t) * h_lists.size(), cudaMemcpyHostToDevice, e->stream));
+      GT_CUDA(cudaStreamSynchronize(e->stream));
+      fs->small_ok = true;
+    }
+  }
   GT_CUDA(cudaEventRecord(ev1, e->stream));
   GT_CUDA(cudaStreamSynchronize(e->stream));
   float ms = 0;
@@ -319,6 +360,86 @@ size_t hist_cells_for_depth(int D, int groups) {
   return cells * (size_t)groups * gt::kBins * gt::kLanes;
 }
 
+// The shared-memory-resident regime: ONE cooperative launch evaluates every individual (small.cu).
+int eval_small(gt_engine* e, FoldSet* fs, int n_ind, const double* genes, const gt_fit_opts* o, double* fitness_out,
+               int32_t* rounds_out, const gt_dump* dump) {
+  const int nfold = o->nfold;
+  const int64_t n = e->n;
+  int64_t ntmax = 0;
+  for (int k = 0; k < nfold; ++k) ntmax = std::max(ntmax, fs->ntrain[k]);
+  const int nt_stride = (int)((ntmax + 31) / 32 * 32);
+  const int smem = gt::small_smem_bytes((int)n, nt_stride);
+  const int max_teams = gt::small_max_teams(nfold, smem);
+  if (max_teams < 1) return fail(GT_ERR_CUDA, "the shared-memory-resident kernel cannot hold a team of %d folds on this device", nfold);
+  const int n_teams = std::min(n_ind, max_teams), n_ctas = n_teams * nfold;
+  // most expensive first: long fits (small eta, deep trees) must not be the last ones started
+  std::vector<int> order(n_ind);
+  for (int i = 0; i < n_ind; ++i) order[i] = i;
+  std::stable_sort(order.begin(), order.end(), [&](int a, int b) {
+    const double* ga = genes + (size_t)a * GT_NUM_GENES; const double* gb = genes + (size_t)b * GT_NUM_GENES;
+    const double ca = ga[2] / std::max(ga[0], 1e-3), cb = gb[2] / std::max(gb[0], 1e-3);
+    return ca > cb;
+  });
+  std::vector<gt::JobParams> h_jp((size_t)n_ind * nfold);
+  std::vector<gt::IndState> h_is(n_ind);
+  for (int q = 0; q < n_ind; ++q) {
+    const double* g = genes + (size_t)q * GT_NUM_GENES;
+    memset(&h_is[q], 0, sizeof(gt::IndState));
+    h_is[q].active = 1; h_is[q].out_index = q;
+    for (int k = 0; k < nfold; ++k) {
+      gt::JobParams& p = h_jp[(size_t)q * nfold + k];
+      memset(&p, 0, sizeof(p));
+      p.eta = (float)g[0]; p.mcw = (float)g[1]; p.max_depth = (int)g[2]; p.gamma = (float)g[3]; p.mds = (float)g[4];
+      p.subsample = (float)g[5]; p.coltree = (float)g[6]; p.collevel = (float)g[7]; p.lambda = (float)g[8];
+      p.alpha = (float)g[9]; p.spw = (float)g[10];
+      p.fold = k; p.ind = q;
+      p.base_margin = base_margin_for(*fs, k, o->objective, p.spw);
+    }
+  }
+  SmallBuffers& B = e->small;
+  const bool want_trace = dump && dump->trace_means;
+  GT_CUDA(B.d_jp.ensure(h_jp.size())); GT_CUDA(B.d_is.ensure(n_ind));
+  GT_CUDA(B.d_nodes.ensure((size_t)n_ctas * gt::kNodeCap)); GT_CUDA(B.d_tree.ensure((size_t)n_ctas * gt::kNodeCap));
+  GT_CUDA(B.d_lists.ensure((size_t)n_ctas * 2 * e->f * nt_stride));
+  GT_CUDA(B.d_fold_s.ensure((size_t)n_teams * 2 * nfold)); GT_CUDA(B.d_bar.ensure(n_teams)); GT_CUDA(B.d_team_ind.ensure((size_t)n_teams * 2));
+  GT_CUDA(B.d_queue.ensure(1)); GT_CUDA(B.d_order.ensure(n_ind)); GT_CUDA(B.d_fit.ensure(n_ind)); GT_CUDA(B.d_rounds.ensure(n_ind));
+  if (want_trace) GT_CUDA(B.d_trace.ensure((size_t)n_ind * o->num_boost_round));
+  GT_CUDA(cudaMemcpyAsync(B.d_jp.p, h_jp.data(), sizeof(gt::JobParams) * h_jp.size(), cudaMemcpyHostToDevice, e->stream));
+  GT_CUDA(cudaMemcpyAsync(B.d_is.p, h_is.data(), sizeof(gt::IndState) * n_ind, cudaMemcpyHostToDevice, e->stream));
+  GT_CUDA(cudaMemcpyAsync(B.d_order.p, order.data(), sizeof(int) * n_ind, cudaMemcpyHostToDevice, e->stream));
+  GT_CUDA(cudaMemsetAsync(B.d_bar.p, 0, sizeof(unsigned) * n_teams, e->stream));
+  GT_CUDA(cudaMemsetAsync(B.d_queue.p, 0, sizeof(int), e->stream));
+  GT_CUDA(cudaMemsetAsync(B.d_nodes.p, 0, sizeof(gt::Node) * (size_t)n_ctas * gt::kNodeCap, e->stream));
+  GT_CUDA(cudaMemsetAsync(B.d_fit.p, 0xff, sizeof(double) * n_ind, e->stream));   // NaN until written
+  GT_CUDA(cudaMemsetAsync(B.d_rounds.p, 0, sizeof(int) * n_ind, e->stream));
+  if (want_trace) GT_CUDA(cudaMemsetAsync(B.d_trace.p, 0xff, sizeof(double) * (size_t)n_ind * o->num_boost_round, e->stream));
+  gt::SmallWave w;
+  memset(&w, 0, sizeof(w));
+  w.n_inds = n_ind; w.nfold = nfold; w.n = (int)n; w.f = e->f; w.fpad = e->fpad; w.nt_stride = nt_stride;
+  w.objective = o->objective; w.metric = o->metric; w.num_boost_round = o->num_boost_round; w.early_stopping_rounds = o->early_stopping_rounds;
+  w.folds = fs->d_folds.p; w.base_lists = fs->d_small_lists.p; w.jp = B.d_jp.p; w.is = B.d_is.p; w.nodes = B.d_nodes.p; w.tree = B.d_tree.p;
+  w.lists = B.d_lists.p; w.fold_s = B.d_fold_s.p; w.team_bar = B.d_bar.p; w.team_ind = B.d_team_ind.p; w.queue = B.d_queue.p;
+  w.order = B.d_order.p; w.trace = want_trace ? B.d_trace.p : nullptr; w.fitness_out = B.d_fit.p; w.rounds_out = B.d_rounds.p;
+  cudaEvent_t e0, e1;
+  GT_CUDA(cudaEventCreate(&e0)); GT_CUDA(cudaEventCreate(&e1));
+  struct EventGuard { cudaEvent_t a, b; ~EventGuard() { cudaEventDestroy(a); cudaEventDestroy(b); } } ev_guard{e0, e1};
+  GT_CUDA(cudaEventRecord(e0, e->stream));
+  const int lrc = gt::launch_small_cv(w, n_teams, smem, e->stream);
+  if (lrc != 0) return fail(GT_ERR_CUDA, "cooperative launch of the shared-memory-resident kernel failed: %s", cudaGetErrorString((cudaError_t)lrc));
+  GT_CUDA(cudaEventRecord(e1, e->stream));
+  GT_CUDA(cudaMemcpyAsync(fitness_out, B.d_fit.p, sizeof(double) * n_ind, cudaMemcpyDeviceToHost, e->stream));
+  std::vector<int> h_rounds(n_ind);
+  GT_CUDA(cudaMemcpyAsync(h_rounds.data(), B.d_rounds.p, sizeof(int) * n_ind, cudaMemcpyDeviceToHost, e->stream));
+  GT_CUDA(cudaStreamSynchronize(e->stream));
+  if (rounds_out) for (int i = 0; i < n_ind; ++i) rounds_out[i] = h_rounds[i];
+  if (want_trace) GT_CUDA(cudaMemcpy(dump->trace_means, B.d_trace.p, sizeof(double) * (size_t)n_ind * o->num_boost_round, cudaMemcpyDeviceToHost));
+  float ms = 0;
+  GT_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+  e->stats.eval_ms = ms; e->stats.hist_ms = 0; e->stats.hist_launches = 0; e->stats.kernel_launches = 1;
+  e->stats.waves = 1; e->stats.jobs = (int64_t)n_ind * nfold; e->stats.hist_row_features = 0; e->stats.hist_alg_bytes = 0;
+  return GT_OK;
+}
+
 int eval_impl(gt_engine* e, int n_ind, const double* genes, const gt_fit_opts* o, double* fitness_out,
               int32_t* rounds_out, const gt_dump* dump) {
   if (!e || !genes || !o || !fitness_out || n_ind < 0) return fail(GT_ERR_ARG, "null argument");
@@ -339,6 +460,10 @@ int eval_impl(gt_engine* e, int n_ind, const double* genes, const gt_fit_opts* o
   FoldSet* fs = nullptr;
   int rc = prepare_impl(e, o->nfold, &fs);
   if (rc != GT_OK) return rc;
+  // small data: the whole fit of a job runs inside one persistent CTA (tree / row-set dumps exist only in the
+  // streaming kernels, so a call that asks for them takes those)
+  if (fs->small_ok && !e->force_streaming && !(dump && (dump->trees || dump->row_sets)))
+    return eval_small(e, fs, n_ind, genes, o, fitness_out, rounds_out, dump);
   const int nfold = o->nfold;
   const int64_t n = e->n;
   int64_t ntmax = 0;
@@ -670,6 +795,7 @@ int create_impl(const HostMatrix* hm, const float* X_dev_or_null, int64_t n, int
   if (e->device < 0 || e->device >= count) return fail(GT_ERR_ARG, "device %d out of range (%d devices)", e->device, count);
   e->mem_budget = opts ? opts->mem_budget_bytes : 0;
   e->collect_timing = opts ? opts->reserved[0] : 0;
+  e->force_streaming = (opts ? opts->reserved[1] : 0) || getenv("GENTUN_B200_NO_SMALL") != nullptr;
   e->n = n; e->f = f; e->ldx = ldx;
   e->fpad = (f + gt::kLanes - 1) / gt::kLanes * gt::kLanes;
   e->groups = e->fpad / gt::kLanes;

@@ -59,6 +59,10 @@ __host__ __device__ inline int part_items_bound(const Wave& w, int level) {
   long long b = (w.nt_stride + kPartRows - 1) / kPartRows + (1ll << level);
   return (int)(b < w.part_cap ? b : w.part_cap);
 }
+// small.cu
+int small_smem_bytes(int n, int nt_stride);
+int small_max_teams(int nfold, int smem_bytes);   // teams of nfold CTAs that can be co-resident (0 on failure)
+int launch_small_cv(const SmallWave& w, int n_teams, int smem_bytes, cudaStream_t s);   // returns cudaError_t
 int hist_smem_bytes();
 int configure_kernels();   // cudaFuncSetAttribute for the dynamic-smem kernels; returns cudaError_t
 

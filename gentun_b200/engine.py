@@ -161,13 +161,14 @@ def fit_opts(booster="gbtree", objective="reg:linear", eval_metric="rmse", nfold
 class Engine(object):
     """One dataset resident on one GPU: replaces the per-individual xgb.DMatrix + xgb.cv set-up."""
 
-    def __init__(self, x, y, device=0, mem_budget_bytes=0, collect_timing=False, device_pointers=None):
+    def __init__(self, x, y, device=0, mem_budget_bytes=0, collect_timing=False, device_pointers=None, streaming_only=False):
         self._lib = load_library()
         self._h = C.c_void_p()
         opts = DataOpts()
         opts.device = int(device)
         opts.mem_budget_bytes = int(mem_budget_bytes)
         opts.reserved[0] = 1 if collect_timing else 0
+        opts.reserved[1] = 1 if streaming_only else 0   # never the shared-memory-resident kernel (regime comparison tests)
         if device_pointers is not None:
             xp, yp, n, f, ldx = device_pointers
             opts.x_on_device = 1

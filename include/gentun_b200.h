@@ -43,7 +43,9 @@ typedef struct {
   int32_t device;           /* CUDA ordinal */
   int32_t x_on_device;      /* 0: X, y are host pointers (copied H2D); 1: already device pointers */
   int64_t mem_budget_bytes; /* 0 = 85% of free device memory at eval time */
-  int32_t reserved[4];
+  int32_t reserved[4];      /* [0] != 0: time the histogram kernel with CUDA events (gt_stats.hist_ms);
+                               [1] != 0: always use the streaming kernels, even for data small enough for the
+                               shared-memory-resident kernel (tests compare the two regimes); rest 0 */
 } gt_data_opts;
 
 /* The non-tuned parameters XgboostIndividual forwards (individuals.py:158-160, 208-216). */
