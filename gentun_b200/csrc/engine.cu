@@ -436,7 +436,8 @@ int eval_small(gt_engine* e, FoldSet* fs, int n_ind, const double* genes, const 
   float ms = 0;
   GT_CUDA(cudaEventElapsedTime(&ms, e0, e1));
   e->stats.eval_ms = ms; e->stats.hist_ms = 0; e->stats.hist_launches = 0; e->stats.kernel_launches = 1;
-  e->stats.waves = 1; e->stats.jobs = (int64_t)n_ind * nfold; e->stats.hist_row_features = 0; e->stats.hist_alg_bytes = 0;
+  e->stats.waves = (n_ind + n_teams - 1) / n_teams;   // how many individuals the busiest team takes from the queue
+  e->stats.jobs = (int64_t)n_ind * nfold; e->stats.hist_row_features = 0; e->stats.hist_alg_bytes = 0;
   return GT_OK;
 }
 
@@ -880,11 +881,17 @@ int gt_engine_eval_ex(gt_engine* e, int32_t n_ind, const double* genes, const gt
 #ifdef GT_SCAN_STATS
 extern "C" void dump_scan_stats();
 #endif
+#ifdef GT_SMALL_PROF
+extern "C" void dump_small_prof();
+#endif
 void gt_engine_destroy(gt_engine* e) {
 #ifdef GT_SCAN_STATS
   dump_scan_stats();
 #endif
   if (!e) return;
+#ifdef GT_SMALL_PROF
+  dump_small_prof();
+#endif
   cudaSetDevice(e->device);
   if (e->stream) { cudaStreamSynchronize(e->stream); }
   e->foldsets.clear();

@@ -21,9 +21,19 @@
 #include "common.cuh"
 #include "kernels.h"
 #include "split.cuh"
+#include <cstdio>
 
 namespace gt {
 namespace {
+
+#ifdef GT_SMALL_PROF   // experiment builds: cycles of CTA 0 by phase
+__device__ unsigned long long g_small_prof[16];
+#define PROF_COUNT(i) atomicAdd(&g_small_prof[i], 1ull)
+#define PROF_MARK(i) do { if (blockIdx.x == 0 && threadIdx.x == 0) { const long long now__ = clock64(); g_small_prof[i] += (unsigned long long)(now__ - prof_t); prof_t = now__; } } while (0)
+#else
+#define PROF_MARK(i)
+#define PROF_COUNT(i)
+#endif
 
 constexpr int kST = kSmallThreads;
 constexpr int kSlots = 1 << (kMaxDepth - 1);       // nodes of the deepest evaluated level
@@ -65,6 +75,17 @@ __device__ __forceinline__ void block_excl_scan2(int a, int b, int& pa, int& pb,
   __syncthreads();
   pa = ia - a + s_w[wid]; pb = ib - b + s_w[32 + wid];
   __syncthreads();   // scratch may be reused at once
+}
+
+// exact gain of one candidate as a sortable key (0: not valid or not positive).  Larger gain first, then the earlier
+// (feature, bin).  One out-of-line copy: the double-precision code is long and only a few candidates get here.
+__device__ __noinline__ unsigned long long exact_key(const JobParams& jp, int Gt, int Ht, float rg, int GL, int HL, int f, int bin,
+                                                     double inv_sg, double inv_sh) {
+  const ChildTot t{(long long)Gt, (long long)Ht, rg};
+  Cand one{0.0f, -1, -1, 0, 0};
+  exact_candidate(one, jp, t, (long long)GL, (long long)HL, f, bin, inv_sg, inv_sh);
+  if (one.f < 0) return 0ull;
+  return ((unsigned long long)__float_as_uint(one.chg) << 32) | (0xffffffffu - (((unsigned)f << 8) | (unsigned)bin));
 }
 
 __device__ __forceinline__ void team_barrier(unsigned* bar, unsigned& target, int nfold) {
@@ -126,6 +147,9 @@ __global__ void __launch_bounds__(kST, 2) k_small_cv(SmallWave w) {
   const uint32_t* base_lists = w.base_lists + (size_t)fold * F * w.nt_stride;
   const int pred_chunks = (n + kPredRows - 1) / kPredRows;
   int parity = 0;
+#ifdef GT_SMALL_PROF
+  long long prof_t = clock64();
+#endif
 
   for (;;) {
     // ---- next individual of the team
@@ -175,7 +199,9 @@ __global__ void __launch_bounds__(kST, 2) k_small_cv(SmallWave w) {
       const double inv_sg = 1.0 / (double)sg, inv_sh = 1.0 / (double)sh;
       const float isg = (float)inv_sg, ish = (float)inv_sh;
       const long long hmin_q = (long long)ceil((double)jp.mcw * (double)sh);
+      const int hmin32 = hmin_q > 0x7fffffffll ? 0x7fffffff : (int)hmin_q;   // node sums are below 2^31: a larger bound just means "never"
 
+      PROF_MARK(0);
       // ---- k_grad: objective gradient, row subsampling, quantisation, root sums
       {
         const uint64_t skey = stream_key(1u, (uint32_t)fold, (uint32_t)round, 0u);
@@ -207,10 +233,14 @@ __global__ void __launch_bounds__(kST, 2) k_small_cv(SmallWave w) {
         __syncthreads();
       }
 
-      // ---- tree growth, level by level
+      PROF_MARK(1);
+      // ---- tree growth, level by level.  Inside a level the warps work independently, one feature each: a warp sweeps
+      // its feature's list in tiles of 32 consecutive elements (warp scans, no block barriers), so a level costs a handful
+      // of barriers whatever the number of features.
       int m = 1;                                  // nodes of the level (slots)
       const uint32_t* cur = base_lists;           // level 0 reads the fold's base lists; later levels ping-pong
       int pp = 0;
+      const int n_iters = (ntrain + 127) / 128;
       for (int level = 0; level < jp.max_depth && m > 0; ++level) {
         // feature sets (k_plan_hist): colsample_bytree once per tree, colsample_bylevel at every level
         if (level == 0) {
@@ -235,105 +265,127 @@ __global__ void __launch_bounds__(kST, 2) k_small_cv(SmallWave w) {
           sample_mask(stream_key(3u, (uint32_t)fold, (uint32_t)round, (uint32_t)level), s_tmask, F, n_lvl, s_lmask);
         } else {
           for (int k = tid; k < kMaskWords; k += kST) s_lmask[k] = s_tmask[k];
-          __syncthreads();
         }
-        for (int s = tid; s < m; s += kST) { S.amax[s] = 0u; S.key[s] = 0ull; S.bG[s] = 0; S.bH[s] = 0; }
+        for (int s = tid; s < m; s += kST) { S.amax[s] = 0u; S.key[s] = 0ull; S.bG[s] = 0; S.bH[s] = 0; S.totL[s] = 0; }
         __syncthreads();
 
-        // ---- split search: one pass per feature of the level's set
-        for (int f = 0; f < F; ++f) {
-          if (!((s_lmask[f >> 5] >> (f & 31)) & 1u)) continue;            // block-uniform
-          const uint32_t* lst = cur + (size_t)f * w.nt_stride;
-          const int i0 = tid * C;
-          uint32_t e[8];
-          int pg[8], ph[8];
-          int tg = 0, th = 0;
+        PROF_MARK(2);
+        // ---- split search.  The prefix sums of a list run over ALL its rows; what lies in front of a node's segment
+        // (the same rows for every feature, hence the same sums) is noted when the sweep enters the segment.
+        for (int f = wid; f < F; f += kST / 32) {
+          if (!((s_lmask[f >> 5] >> (f & 31)) & 1u)) continue;            // warp-uniform
+          const uint4* lst4 = reinterpret_cast<const uint4*>(cur + (size_t)f * w.nt_stride);
+          int carry_g = 0, carry_h = 0;
+          uint4 q_next = lane * 4 < ntrain ? lst4[lane] : make_uint4(0u, 0u, 0u, 0u);
+          for (int it = 0; it < n_iters; ++it) {
+            // a lane takes 4 consecutive elements: its own running sums first, one warp scan per 128 elements
+            const int i0 = it * 128 + lane * 4;
+            const uint4 q = q_next;
+            q_next = (i0 + 128 < ntrain) ? lst4[(it + 1) * 32 + lane] : make_uint4(0u, 0u, 0u, 0u);   // on its way while this one is worked
+            const uint32_t e[4] = {q.x, q.y, q.z, q.w};
+            int pg[4], ph[4];
+            uint16_t sl[4];
+            int tg = 0, th = 0;
 #pragma unroll
-          for (int c = 0; c < 8; ++c) {
-            e[c] = 0u; pg[c] = 0; ph[c] = 0;
-            if (c < C && i0 + c < ntrain) {
-              e[c] = lst[i0 + c];
-              const int2 gh = s_gq[e[c] & 0xffffu];
+            for (int k = 0; k < 4; ++k) {
+              const bool have = i0 + k < ntrain;
+              const int row = (int)(e[k] & 0xffffu);
+              const int2 gh = have ? s_gq[row] : make_int2(0, 0);
+              sl[k] = have ? s_pos[row] : kNoSlot;
               tg += gh.x; th += gh.y;
-              pg[c] = tg; ph[c] = th;                                      // inclusive, chunk-local
+              pg[k] = tg; ph[k] = th;
             }
-          }
-          s_firstbin[tid] = (uint16_t)(e[0] >> 16);
-          if (tid == 0) s_firstbin[kST] = 0;
-          int og, oh;
-          block_excl_scan2(tg, th, og, oh, s_scr);
-          // prefix in front of every node's segment (the same for every feature: the same rows precede it)
+            const int og = warp_incl_scan(tg) - tg + carry_g, oh = warp_incl_scan(th) - th + carry_h;
+            carry_g = __shfl_sync(0xffffffffu, og + tg, 31); carry_h = __shfl_sync(0xffffffffu, oh + th, 31);
 #pragma unroll
-          for (int c = 0; c < 8; ++c) {
-            if (c < C && i0 + c < ntrain) {
-              const uint16_t sl = s_pos[e[c] & 0xffffu];
-              if (sl != kNoSlot && i0 + c == S.beg[sl]) {
-                const int2 gh = s_gq[e[c] & 0xffffu];
-                S.baseG[sl] = og + pg[c] - gh.x; S.baseH[sl] = oh + ph[c] - gh.y;
+            for (int k = 0; k < 4; ++k) {
+              pg[k] += og; ph[k] += oh;
+              if (sl[k] != kNoSlot && i0 + k == S.beg[sl[k]]) {
+                const int2 gh = s_gq[e[k] & 0xffffu];
+                S.baseG[sl[k]] = pg[k] - gh.x; S.baseH[sl[k]] = ph[k] - gh.y;
               }
             }
-          }
-          __syncthreads();
-          // stage 1: fp32 estimate of every candidate (last row of a run of equal bins, not the node's last row)
-          float est[8];
-          int cGL[8], cHL[8];
+            __syncwarp();
+            uint32_t nb_lane = __shfl_down_sync(0xffffffffu, e[0] >> 16, 1);
+            const uint32_t nb_iter = __shfl_sync(0xffffffffu, q_next.x, 0) >> 16;
+            if (lane == 31) nb_lane = nb_iter;
 #pragma unroll
-          for (int c = 0; c < 8; ++c) {
-            est[c] = -1.0f;
-            if (c < C && i0 + c < ntrain) {
-              const uint16_t sl = s_pos[e[c] & 0xffffu];
-              if (sl != kNoSlot && i0 + c + 1 < S.end[sl]) {
-                const uint32_t nb = (c + 1 < C) ? (e[(c + 1) & 7] >> 16) : (uint32_t)s_firstbin[tid + 1];
-                if (nb != (e[c] >> 16)) {
-                  const int GL = og + pg[c] - S.baseG[sl], HL = oh + ph[c] - S.baseH[sl];
-                  const int Ht = S.Ht[sl];
-                  cGL[c] = GL; cHL[c] = HL;
-                  if ((long long)HL >= hmin_q && (long long)(Ht - HL) >= hmin_q) {
-                    const float Gt_f = (float)S.Gt[sl] * isg, Ht_f = (float)Ht * ish;
-                    const float glf = (float)GL * isg, hlf = (float)HL * ish;
-                    const float v = mds_on ? split_est<true>(gk, glf, hlf, Gt_f - glf, Ht_f - hlf)
-                                           : split_est<false>(gk, glf, hlf, Gt_f - glf, Ht_f - hlf);
-                    est[c] = fmaxf(v, 0.0f);
-                    atomicMax(&S.amax[sl], __float_as_uint(est[c]));
+            for (int k = 0; k < 4; ++k) {
+              const uint32_t bin = e[k] >> 16;
+              const uint32_t nb = k < 3 ? (e[(k + 1) & 3] >> 16) : nb_lane;
+              const uint16_t slk = sl[k];
+              // a candidate: the last row of a run of equal bins that is not the node's last row
+              if (slk != kNoSlot && i0 + k + 1 < S.end[slk] && nb != bin) {
+                const int GL = pg[k] - S.baseG[slk], HL = ph[k] - S.baseH[slk];
+                const int Ht = S.Ht[slk];
+                if (HL >= hmin32 && Ht - HL >= hmin32) {
+                  // stage 1: fp32 estimate; stage 2: exact gain (reference expression order) if the estimate is within
+                  // its own error of the best estimate seen so far for the node -- a bound that only rises, so nothing
+                  // that could win is skipped
+                  const float Gt_f = (float)S.Gt[slk] * isg, Ht_f = (float)Ht * ish;
+                  const float glf = (float)GL * isg, hlf = (float)HL * ish;
+                  const float v = mds_on ? split_est<true>(gk, glf, hlf, Gt_f - glf, Ht_f - hlf)
+                                         : split_est<false>(gk, glf, hlf, Gt_f - glf, Ht_f - hlf);
+                  PROF_COUNT(12);
+                  const float est = fmaxf(v, 0.0f);
+                  const float seen = __uint_as_float(S.amax[slk]);             // may be stale: any lower bound of the final maximum will do
+                  if (est > seen) atomicMax(&S.amax[slk], __float_as_uint(est));
+                  const float amax = fmaxf(seen, est), rg = S.root_gain[slk];
+                  const float margin = 3.2e-5f * (amax + fabsf(rg)) + 1e-12f;
+                  if (est >= fmaxf(amax, rg) - 2.0f * margin) {
+                    PROF_COUNT(13);
+                    const unsigned long long key = exact_key(jp, S.Gt[slk], Ht, rg, GL, HL, f, (int)bin, inv_sg, inv_sh);
+                    if (key) atomicMax(&S.key[slk], key);
                   }
                 }
               }
             }
           }
-          __syncthreads();
-          // stage 2: exact gain (reference expression order) of the candidates within the estimate's error of the best
-          unsigned long long mykey[8];
-#pragma unroll
-          for (int c = 0; c < 8; ++c) {
-            mykey[c] = 0ull;
-            if (est[c] >= 0.0f) {
-              const uint16_t sl = s_pos[e[c] & 0xffffu];
-              const float amax = __uint_as_float(S.amax[sl]), rg = S.root_gain[sl];
-              const float margin = 3.2e-5f * (fmaxf(amax, 0.f) + fabsf(rg)) + 1e-12f;
-              const float cut = fmaxf(amax, rg) - 2.0f * margin;
-              if (est[c] >= cut) {
-                const ChildTot t{(long long)S.Gt[sl], (long long)S.Ht[sl], rg};
-                Cand one{0.0f, -1, -1, 0, 0};
-                exact_candidate(one, jp, t, (long long)cGL[c], (long long)cHL[c], f, (int)(e[c] >> 16), inv_sg, inv_sh);
-                if (one.f >= 0) {     // finite and > 0
-                  mykey[c] = ((unsigned long long)__float_as_uint(one.chg) << 32) | (0xffffffffu - (((unsigned)f << 8) | (e[c] >> 16)));
-                  atomicMax(&S.key[sl], mykey[c]);
-                }
-              }
-            }
-          }
-          __syncthreads();
-#pragma unroll
-          for (int c = 0; c < 8; ++c) {
-            if (mykey[c] != 0ull) {
-              const uint16_t sl = s_pos[e[c] & 0xffffu];
-              if (S.key[sl] == mykey[c]) { S.bG[sl] = cGL[c]; S.bH[sl] = cHL[c]; }
-            }
-          }
-          // (the next feature's first barrier orders these writes before anything reads them)
         }
         __syncthreads();
 
+        PROF_MARK(3);
+        // ---- the winning candidate of every node: which rows go left, and their sums (GL, HL, count)
+        {
+          uint8_t bv[8];
+          uint16_t slv[8];
+          unsigned lov[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {        // all the gathers of this thread's rows first, then their use
+            const int r = k * kST + tid;
+            slv[k] = kNoSlot; lov[k] = 0u; bv[k] = 255;
+            if (r < ntrain) {
+              slv[k] = s_pos[r];
+              if (slv[k] != kNoSlot && S.key[slv[k]] != 0ull) {
+                lov[k] = 0xffffffffu - (unsigned)(S.key[slv[k]] & 0xffffffffull);
+                bv[k] = fd.bins[(size_t)r * fpad + (lov[k] >> 8)];
+              } else {
+                slv[k] = kNoSlot;
+              }
+            }
+          }
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const int r = k * kST + tid;
+            if (k * kST >= ntrain) break;                                  // block-uniform
+            const uint16_t sl = slv[k];
+            const int l = (sl != kNoSlot && (unsigned)bv[k] <= (lov[k] & 255u)) ? 1 : 0;
+            int2 gh = make_int2(0, 0);
+            if (r < ntrain) { s_left[r] = (uint8_t)l; if (l) gh = s_gq[r]; }
+            // rows of a warp mostly belong to one node at the top levels: one atomic per warp then, one per row otherwise
+            const uint16_t sl0 = (uint16_t)__shfl_sync(0xffffffffu, (unsigned)sl, 0);
+            if (__all_sync(0xffffffffu, sl == sl0)) {
+              const int sg2 = __reduce_add_sync(0xffffffffu, gh.x), sh2 = __reduce_add_sync(0xffffffffu, gh.y);
+              const int sc = __reduce_add_sync(0xffffffffu, l);
+              if (lane == 0 && sl0 != kNoSlot && sc) { atomicAdd(&S.bG[sl0], sg2); atomicAdd(&S.bH[sl0], sh2); atomicAdd(&S.totL[sl0], sc); }
+            } else if (l) {
+              atomicAdd(&S.bG[sl], gh.x); atomicAdd(&S.bH[sl], gh.y); atomicAdd(&S.totL[sl], 1);
+            }
+          }
+        }
+        __syncthreads();
+
+        PROF_MARK(4);
         // ---- settle the level's nodes (CPUExpandEntry::IsValid), create children
         for (int s = tid; s < m; s += kST) {
           const int node = S.node[s];
@@ -357,69 +409,59 @@ __global__ void __launch_bounds__(kST, 2) k_small_cv(SmallWave w) {
         any = __syncthreads_or(any);
         if (!any || level + 1 >= jp.max_depth) { m = 0; break; }
 
-        // ---- stable partition of every live feature's list (partition_builder.h), node by node in place
-        for (int r = tid; r < ntrain; r += kST) {
-          const uint16_t sl = s_pos[r];
-          uint8_t l = 0;
-          if (sl != kNoSlot && S.sfeat[sl] >= 0) l = fd.bins[(size_t)r * fpad + S.sfeat[sl]] <= S.sbin[sl] ? 1 : 0;
-          s_left[r] = l;
-        }
-        __syncthreads();
+        PROF_MARK(5);
+        // ---- stable partition of every live feature's list (partition_builder.h), node by node in place; a warp per
+        // feature again.  Lefts in front of a segment: noted on entering it, like the sums above.
         uint32_t* nxt = lists + (size_t)pp * F * w.nt_stride;
-        bool first = true;
-        for (int f = 0; f < F; ++f) {
+        for (int f = wid; f < F; f += kST / 32) {
           if (!((s_tmask[f >> 5] >> (f & 31)) & 1u)) continue;            // features outside the tree's set are never read again
-          const uint32_t* lst = cur + (size_t)f * w.nt_stride;
+          const uint4* lst4 = reinterpret_cast<const uint4*>(cur + (size_t)f * w.nt_stride);
           uint32_t* out = nxt + (size_t)f * w.nt_stride;
-          const int i0 = tid * C;
-          uint32_t e[8];
-          int pl[8];
-          int tl = 0;
+          int carry = 0;
+          uint4 q_next = lane * 4 < ntrain ? lst4[lane] : make_uint4(0u, 0u, 0u, 0u);
+          for (int it = 0; it < n_iters; ++it) {
+            const int i0 = it * 128 + lane * 4;
+            const uint4 q = q_next;
+            q_next = (i0 + 128 < ntrain) ? lst4[(it + 1) * 32 + lane] : make_uint4(0u, 0u, 0u, 0u);
+            const uint32_t e[4] = {q.x, q.y, q.z, q.w};
+            int pl[4], lk[4];
+            uint16_t sl[4];
+            int tl = 0;
 #pragma unroll
-          for (int c = 0; c < 8; ++c) {
-            e[c] = 0u; pl[c] = 0;
-            if (c < C && i0 + c < ntrain) {
-              e[c] = lst[i0 + c];
-              pl[c] = tl;                                                  // exclusive, chunk-local
-              tl += s_left[e[c] & 0xffffu];
+            for (int k = 0; k < 4; ++k) {
+              const int row = (int)(e[k] & 0xffffu);
+              sl[k] = (i0 + k < ntrain) ? s_pos[row] : kNoSlot;
+              if (sl[k] != kNoSlot && S.sfeat[sl[k]] < 0) sl[k] = kNoSlot;     // node not partitioned: rows stay where they are
+              lk[k] = sl[k] != kNoSlot ? (int)s_left[row] : 0;
+              pl[k] = tl;                                                      // exclusive, lane-local
+              tl += lk[k];
             }
-          }
-          int ol, dummy;
-          block_excl_scan2(tl, 0, ol, dummy, s_scr);
-          if (first) {     // lefts in front of each segment and inside it: the same for every feature
+            const int ol = warp_incl_scan(tl) - tl + carry;
+            carry = __shfl_sync(0xffffffffu, ol + tl, 31);
 #pragma unroll
-            for (int c = 0; c < 8; ++c) {
-              if (c < C && i0 + c < ntrain) {
-                const uint16_t sl = s_pos[e[c] & 0xffffu];
-                if (sl != kNoSlot && S.sfeat[sl] >= 0) {
-                  if (i0 + c == S.beg[sl]) S.baseL[sl] = ol + pl[c];
-                  if (i0 + c == S.end[sl] - 1) S.totL[sl] = ol + pl[c] + s_left[e[c] & 0xffffu];     // inclusive count; base subtracted below
+            for (int k = 0; k < 4; ++k) {
+              pl[k] += ol;
+              if (sl[k] != kNoSlot && i0 + k == S.beg[sl[k]]) S.baseL[sl[k]] = pl[k];
+            }
+            __syncwarp();
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              if (i0 + k < ntrain) {
+                int dest = i0 + k;
+                if (sl[k] != kNoSlot) {
+                  const int beg = S.beg[sl[k]], rankL = pl[k] - S.baseL[sl[k]];
+                  dest = lk[k] ? beg + rankL : beg + S.totL[sl[k]] + (i0 + k - beg - rankL);
                 }
+                out[dest] = e[k];
               }
-            }
-            __syncthreads();
-            for (int s = tid; s < m; s += kST) if (S.sfeat[s] >= 0) S.totL[s] -= S.baseL[s];
-            __syncthreads();
-            first = false;
-          }
-#pragma unroll
-          for (int c = 0; c < 8; ++c) {
-            if (c < C && i0 + c < ntrain) {
-              const int row = e[c] & 0xffffu;
-              const uint16_t sl = s_pos[row];
-              int dest = i0 + c;
-              if (sl != kNoSlot && S.sfeat[sl] >= 0) {
-                const int beg = S.beg[sl], rankL = ol + pl[c] - S.baseL[sl];
-                dest = s_left[row] ? beg + rankL : beg + S.totL[sl] + (i0 + c - beg - rankL);
-              }
-              out[dest] = e[c];
             }
           }
         }
         __syncthreads();
+        PROF_MARK(6);
         // ---- next level's nodes: the open children, in node order
         {
-          int mine = 0;       // open children of the slots this thread owns (slot = tid, one per thread: kSlots <= kST)
+          int mine = 0;       // open children of the slot this thread owns (slot = tid: kSlots <= kST)
           int lo = 0, ro = 0;
           if (tid < m && S.sfeat[tid] >= 0) {
             const int node = S.node[tid];
@@ -428,12 +470,12 @@ __global__ void __launch_bounds__(kST, 2) k_small_cv(SmallWave w) {
           }
           int off, dummy;
           block_excl_scan2(mine, 0, off, dummy, s_scr);
-          // children records need this slot's values before the slot arrays are overwritten: read, barrier, write
+          // the children's records need this slot's values before the slot arrays are overwritten: read, barrier, write
           int node = 0, beg = 0, end = 0, totL = 0;
           if (tid < m) { node = S.node[tid]; beg = S.beg[tid]; end = S.end[tid]; totL = S.totL[tid]; }
           const bool part = tid < m && S.sfeat[tid] >= 0;
           if (tid == kST - 1) s_i[1] = off + mine;
-          // row -> next slot, through the old slot: stash the two children's new slots in baseG / baseH
+          // row -> next slot, through the old slot: the two children's new slots are stashed in baseG / baseH
           if (tid < m) { S.baseG[tid] = part && lo ? off : -1; S.baseH[tid] = part && ro ? off + lo : -1; }
           __syncthreads();
           for (int r = tid; r < ntrain; r += kST) {
@@ -463,8 +505,10 @@ __global__ void __launch_bounds__(kST, 2) k_small_cv(SmallWave w) {
         }
         cur = nxt;
         pp ^= 1;
+        PROF_MARK(7);
       }
       __syncthreads();
+      PROF_MARK(8);
 
       // ---- k_predict_small: every row walks the new tree on its bin bytes; metric terms in that kernel's order
       for (int i = tid; i < kNodeCap; i += kST) {
@@ -525,6 +569,7 @@ __global__ void __launch_bounds__(kST, 2) k_small_cv(SmallWave w) {
         }
         __syncthreads();
       }
+      PROF_MARK(9);
       // ---- k_round_end: this fold's sum, then the mean over the team's folds
       if (wid == 0) {
         double s = 0.0;
@@ -545,6 +590,7 @@ __global__ void __launch_bounds__(kST, 2) k_small_cv(SmallWave w) {
       }
       __syncthreads();
       const double mean = s_d[0];
+      PROF_MARK(10);
       last_mean = mean; rounds_run = round + 1;
       if (w.early_stopping_rounds > 0) {
         if (round == 0) { best_score = mean; best_iter = 0; }
@@ -565,6 +611,17 @@ __global__ void __launch_bounds__(kST, 2) k_small_cv(SmallWave w) {
 }
 
 }  // namespace
+
+#ifdef GT_SMALL_PROF
+extern "C" void dump_small_prof() {
+  unsigned long long h[16];
+  cudaMemcpyFromSymbol(h, g_small_prof, sizeof(h));
+  const char* names[] = {"round top", "grad", "masks", "search", "left pass", "settle", "partition", "frontier", "tree end", "predict", "round end"};
+  unsigned long long tot = 0; for (int i = 0; i < 11; ++i) tot += h[i];
+  for (int i = 0; i < 11; ++i) fprintf(stderr, "small prof %-10s %6.2f%%  %llu cycles\n", names[i], 100.0 * h[i] / (double)tot, h[i]);
+  fprintf(stderr, "small prof candidates estimated %llu, evaluated exactly %llu (all CTAs)\n", h[12], h[13]);
+}
+#endif
 
 int small_max_teams(int nfold, int smem_bytes) {
   int dev = 0, sms = 0, per_sm = 0;

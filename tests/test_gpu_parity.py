@@ -329,10 +329,10 @@ def test_deterministic_and_wave_independent(wine_np):
     a, _ = eng.evaluate(GENE_SETS, nfold=3, num_boost_round=10)
     b, _ = eng.evaluate(GENE_SETS, nfold=3, num_boost_round=10)
     assert np.array_equal(a, b)
-    small = Engine(x, y, mem_budget_bytes=400 << 20)    # forces several waves
+    small = Engine(x, y, mem_budget_bytes=400 << 20, streaming_only=True)    # streaming kernels, forced into several waves
     c, _ = small.evaluate(GENE_SETS, nfold=3, num_boost_round=10)
     assert small.stats()["waves"] > 1
-    assert np.array_equal(a, c)
+    assert np.array_equal(a, c)                          # (a comes from the shared-memory-resident kernel: same bits)
     one, _ = eng.evaluate(GENE_SETS[3:4], nfold=3, num_boost_round=10)
     assert one[0] == a[3]
     eng.close()
