@@ -23,6 +23,10 @@ namespace gt {
 namespace {
 
 constexpr int kHistSmem = 2 * kBins * kLanes * (int)sizeof(int);   // g plane + h plane = 64 KiB
+#ifndef GT_JOB_FASTEST_LEVELS
+#define GT_JOB_FASTEST_LEVELS 2
+#endif
+constexpr int kJobFastestLevels = GT_JOB_FASTEST_LEVELS;   // k_hist: levels up to this one run the same item of many jobs together
 
 
 // ------------------------------------------------------------------ round set-up / tear-down
@@ -266,7 +270,13 @@ __global__ void __launch_bounds__(256) k_hist_zero(Wave w, int level) {
   const int cells = w.groups * kBins * kLanes;
   for (int z = blockIdx.x; z < js.n_zero; z += gridDim.x) {
     longlong2* h = reinterpret_cast<longlong2*>(node_hist(w, jp, level, zl[z]));
-    for (int i = threadIdx.x; i < cells; i += blockDim.x) h[i] = make_longlong2(0, 0);
+    if (level == 0 && jp.uniform_h) {       // see k_hist: hessian plane = row count x the one quantised hessian
+      const int* cnt = w.folds[jp.fold].count_hist;
+      const long long hq = (long long)__float2int_rn(1.0f * js.sh);
+      for (int i = threadIdx.x; i < cells; i += blockDim.x) h[i] = make_longlong2(0, (long long)cnt[i] * hq);
+    } else {
+      for (int i = threadIdx.x; i < cells; i += blockDim.x) h[i] = make_longlong2(0, 0);
+    }
   }
 }
 
@@ -320,6 +330,7 @@ __device__ __forceinline__ void hist_load(HistStage<UNITS>& st, uint32_t myrow, 
   st.gv = myrow != 0xffffffffu ? gq[myrow] : make_int2(0, 0);
 }
 
+template <bool WITH_H>
 __device__ __forceinline__ void hist_accumulate(const uint4 v, const int2 g2, bool q1, bool q2, int rb, const uint32_t (&cs)[16]) {
   // rotate the 16 bytes right by `rot` bytes: two conditional word rotations, then a funnel shift
   const uint32_t a0 = q1 ? v.y : v.x, a1 = q1 ? v.z : v.y, a2 = q1 ? v.w : v.z, a3 = q1 ? v.x : v.w;
@@ -343,7 +354,7 @@ __device__ __forceinline__ void hist_accumulate(const uint4 v, const int2 g2, bo
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
       red_shared(cell[k], g2.x);
-      red_shared_hi(cell[k], g2.y);
+      if (WITH_H) red_shared_hi(cell[k], g2.y);
     }
   }
 }
@@ -390,16 +401,23 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 2 : 1) k_
   constexpr int kGroupsPerCta = UNITS / 2;
   constexpr uint32_t kStride = (kThreads / 32) * 32u;          // rows per CTA iteration
   constexpr int kEpochIters = kEpochRows / (int)kStride;       // CTA iterations between overflow checks
-  // Grid: x = (job, feature-group slice), y = work item, and x enumerates the level's jobs fold-major (all
-  // individuals of fold 0, then fold 1, ...).  CTAs are dispatched x-fastest, so the CTAs in flight at one time are
-  // the SAME item index of many jobs of ONE fold: at the top levels (row sets still near the identity) they read the
-  // same bin rows, which then come from L2 for all but the first of them.
+  // Grid at the top levels: x = (job, feature-group slice), y = work item, and x enumerates the level's jobs fold-major
+  // (all individuals of fold 0, then fold 1, ...).  CTAs are dispatched x-fastest, so the CTAs in flight at one time
+  // are the SAME item index of many jobs of ONE fold: with row sets still near the identity they read the same bin
+  // rows, which then come from L2 for all but the first of them (level-0 DRAM reads 9.0 -> 2.3 GB on the C3 shape).
   const int ncg = w.groups / kGroupsPerCta;
-  const int lvl_jobs = (int)gridDim.x / ncg, lvl_inds = lvl_jobs / w.nfold;
-  const int jx = (int)blockIdx.x / ncg, cg = (int)blockIdx.x % ncg;
-  const int j = (jx % lvl_inds) * w.nfold + jx / lvl_inds;
+  int j, item_idx, cg;
+  if (level <= kJobFastestLevels) {
+    const int lvl_jobs = (int)gridDim.x / ncg, lvl_inds = lvl_jobs / w.nfold;
+    const int jx = (int)blockIdx.x / ncg;
+    cg = (int)blockIdx.x % ncg;
+    j = (jx % lvl_inds) * w.nfold + jx / lvl_inds;
+    item_idx = blockIdx.y;
+  } else {     // deeper down the jobs' row sets have nothing in common any more: one job's items side by side (measured 2 % faster there)
+    j = blockIdx.y;
+    item_idx = (int)blockIdx.x / ncg; cg = (int)blockIdx.x % ncg;
+  }
   const JobState& js = w.js[j];
-  const int item_idx = blockIdx.y;
   if (item_idx >= js.n_hist_items) return;
   const JobParams& jp = w.jp[j];
   const HistItem it = w.hitems[(size_t)j * w.hist_cap + item_idx];
@@ -430,6 +448,11 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 2 : 1) k_
     asm volatile("mov.u32 %0, %1;" : "=r"(cs[s]) : "r"(v));   // opaque: keep it in a register, never rematerialise
   }
   const bool shared_node = it.flags & 1;
+  // Root of a job whose rows all carry the same hessian (squared error, no row subsampling, no weighted label): the
+  // hessian plane of its histogram is the fold's row COUNT per (feature, bin) times that one value -- the same for
+  // every such job of the fold, counted once when the folds were binned.  k_hist_zero writes it; only the gradient
+  // plane is accumulated here, i.e. half the shared-memory reductions of the level that has the most rows.
+  const bool with_h = !(level == 0 && shared_node && jp.uniform_h);
   Node& node = w.nodes[(size_t)j * kNodeCap + it.node];
   const bool never_early = !shared_node && node.narrow;   // owned narrow node: no cell of it can leave 31 bits
   bool stored = false;                                                     // owned wide node: has an early flush happened
@@ -450,11 +473,20 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 2 : 1) k_
     const uint32_t p2 = my0 + (itn + 2) * kStride;
     row_c = p2 < cnt ? ridx[p2] : 0xffffffffu;
     if (itn + 1 < n_iter) hist_load<UNITS>(nxt, row_b, rslot, bins_unit, gq, fpad);
+    if (with_h) {          // CTA-uniform
 #pragma unroll
-    for (int sb = 0; sb < UNITS; ++sb) {
-      const int src = sb * (32 / UNITS) + rslot;
-      const int2 g2 = make_int2(__shfl_sync(0xffffffffu, cur.gv.x, src), __shfl_sync(0xffffffffu, cur.gv.y, src));
-      hist_accumulate(cur.b[sb], g2, q1, q2, rb, cs);
+      for (int sb = 0; sb < UNITS; ++sb) {
+        const int src = sb * (32 / UNITS) + rslot;
+        const int2 g2 = make_int2(__shfl_sync(0xffffffffu, cur.gv.x, src), __shfl_sync(0xffffffffu, cur.gv.y, src));
+        hist_accumulate<true>(cur.b[sb], g2, q1, q2, rb, cs);
+      }
+    } else {
+#pragma unroll
+      for (int sb = 0; sb < UNITS; ++sb) {
+        const int src = sb * (32 / UNITS) + rslot;
+        const int2 g2 = make_int2(__shfl_sync(0xffffffffu, cur.gv.x, src), 0);
+        hist_accumulate<false>(cur.b[sb], g2, q1, q2, rb, cs);
+      }
     }
     acc_g += (unsigned)abs(cur.gv.x); acc_h += (unsigned)cur.gv.y;   // every lane holds one row of the iteration
     cur = nxt;
@@ -469,6 +501,14 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 2 : 1) k_
       abs_rows += acc_g;
       acc_g = 0u; acc_h = 0u;
       const bool must = __syncthreads_or((run_g >= lim_g || run_h >= lim_h) && !never_early);
+#ifdef GT_HIST_NO_LOOK
+      if (must) {
+        hist_flush<UNITS>(w, jp, level, it, cg, sh, shared_node ? kFlushAtomic : stored ? kFlushAddWide : kFlushStoreWide, true);
+        stored = true;
+        run_g = 0u; run_h = 0u;
+        __syncthreads();
+      }
+#else
       if (must) {
         // The running sums bound every cell as if all rows had fallen into one bin.  Look at the cells themselves:
         // with rows spread over many bins the largest one is far below the bound, and the CTA carries on from there
@@ -494,6 +534,7 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 2 : 1) k_
         run_g = 0u; run_h = 0u;
         __syncthreads();
       }
+#endif
     }
   }
   // the node's exact sum of |g_q| decides the cell format of its children (child_narrow)
@@ -1642,8 +1683,14 @@ void launch_hist_zero(const Wave& w, int level, cudaStream_t s) {
 }
 int launch_hist(const Wave& w, int level, cudaStream_t s) {   // returns the number of kernels launched
   int cap = hist_items_bound(w, level);
-  if (w.groups % 2 == 0) k_hist<4><<<dim3(w.lvl_jobs[level] * (w.groups / 2), cap), 512, 2 * kHistSmem, s>>>(w, level);
-  else k_hist<2><<<dim3(w.lvl_jobs[level] * w.groups, cap), 256, kHistSmem, s>>>(w, level);
+  const int jobs = w.lvl_jobs[level];
+  const bool job_fastest = level <= kJobFastestLevels;
+  if (w.groups % 2 == 0) {
+    const int ncg = w.groups / 2;
+    k_hist<4><<<job_fastest ? dim3(jobs * ncg, cap) : dim3(cap * ncg, jobs), 512, 2 * kHistSmem, s>>>(w, level);
+  } else {
+    k_hist<2><<<job_fastest ? dim3(jobs * w.groups, cap) : dim3(cap * w.groups, jobs), 256, kHistSmem, s>>>(w, level);
+  }
   return 1;
 }
 int launch_scan(const Wave& w, int level, cudaStream_t s) {   // returns the number of kernels launched

@@ -64,6 +64,7 @@ struct JobParams {     // constant over one evaluation
   int max_depth;
   int fold;
   int ind;             // index inside the wave
+  int uniform_h;       // every train row of the fold has the same hessian under this job's genes (see k_hist)
   unsigned long long hist_off[2];   // element offsets of the even / odd level histogram buffers
 };
 
@@ -96,6 +97,7 @@ struct FoldDev {
   const float* y;        // [n] fold order
   const float* cuts;     // [f][256]
   const int* ncuts;      // [f]
+  const int* count_hist; // [groups][256][32] train rows per (feature, bin), laid out like a node histogram
   long long ntrain, ntest;
 };
 

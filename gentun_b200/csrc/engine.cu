@@ -109,6 +109,7 @@ struct FoldSet {
   std::vector<DevBuf<uint8_t>> d_bins;
   std::vector<DevBuf<uint8_t>> d_bins_col;
   std::vector<DevBuf<float>> d_y;
+  std::vector<DevBuf<int>> d_count_hist;      // per fold: train rows per (feature, bin)
   DevBuf<float> d_cuts;                       // [nfold][f][256]
   DevBuf<int> d_ncuts;                        // [nfold][f]
   DevBuf<gt::FoldDev> d_folds;
@@ -184,7 +185,7 @@ int prepare_impl(gt_engine* e, int nfold, FoldSet** out) {
   fs->perm.resize(n); fs->fold_begin.resize(nfold + 1);
   make_folds_host(n, nfold, 0u, fs->perm.data(), fs->fold_begin.data());
   fs->ntrain.resize(nfold); fs->ntest.resize(nfold); fs->rows.resize(nfold);
-  fs->d_rows.resize(nfold); fs->d_bins.resize(nfold); fs->d_bins_col.resize(nfold); fs->d_y.resize(nfold);
+  fs->d_rows.resize(nfold); fs->d_bins.resize(nfold); fs->d_bins_col.resize(nfold); fs->d_y.resize(nfold); fs->d_count_hist.resize(nfold);
   fs->sum_not1_sq.assign(nfold, 0); fs->sum_not1_lg.assign(nfold, 0); fs->n1.assign(nfold, 0); fs->nnot1.assign(nfold, 0);
   cudaEvent_t ev0, ev1;
   GT_CUDA(cudaEventCreate(&ev0)); GT_CUDA(cudaEventCreate(&ev1));
@@ -271,6 +272,12 @@ int prepare_impl(gt_engine* e, int nfold, FoldSet** out) {
     GT_CUDA(cudaGetLastError());
     gt::launch_gather_y(e->d_y, fs->d_rows[k].p, n, fs->d_y[k].p, e->stream);
     GT_CUDA(cudaGetLastError());
+    const size_t hist_cells = (size_t)e->groups * gt::kBins * gt::kLanes;
+    GT_CUDA(fs->d_count_hist[k].ensure(hist_cells));
+    GT_CUDA(cudaMemsetAsync(fs->d_count_hist[k].p, 0, sizeof(int) * hist_cells, e->stream));
+    gt::launch_count_hist(fs->d_bins[k].p, f, e->fpad, fs->ntrain[k], fs->d_count_hist[k].p, e->stream);
+    GT_CUDA(cudaGetLastError());
+    h_folds[k].count_hist = fs->d_count_hist[k].p;
     h_folds[k].bins = fs->d_bins[k].p; h_folds[k].bins_col = fs->d_bins_col[k].p; h_folds[k].y = fs->d_y[k].p;
     h_folds[k].cuts = fs->d_cuts.p + (size_t)k * f * GT_MAX_BIN; h_folds[k].ncuts = fs->d_ncuts.p + (size_t)k * f;
     h_folds[k].ntrain = fs->ntrain[k]; h_folds[k].ntest = fs->ntest[k];
@@ -591,6 +598,7 @@ int eval_impl(gt_engine* e, int n_ind, const double* genes, const gt_fit_opts* o
         p.alpha = (float)g[9]; p.spw = (float)g[10];
         p.fold = k; p.ind = q;
         p.base_margin = base_margin_for(*fs, k, o->objective, p.spw);
+        p.uniform_h = o->objective == GT_OBJ_SQUAREDERROR && p.subsample >= 1.0f && (fs->n1[k] == 0 || p.spw == 1.0f);
         const int last = D - 1;
         const int even = last - (last & 1), odd = last - 1 + (last & 1);
         p.hist_off[0] = hoff; hoff += ((size_t)1 << even) * e->groups * gt::kBins * gt::kLanes;

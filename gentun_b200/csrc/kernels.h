@@ -25,6 +25,7 @@ void launch_bin(const float* X, long long ldx, int f, int fpad, const uint32_t* 
 void launch_bins_to_columns(const uint8_t* bins, int f, int fpad, long long n, uint8_t* out, cudaStream_t s);
 void launch_ingest_tile(const void* tile, int dtype, int colmajor, long long ld, int rows, int f, float* X, long long ldx,
                         long long r0, cudaStream_t s);
+void launch_count_hist(const uint8_t* bins, int f, int fpad, long long ntrain, int* out /* zeroed */, cudaStream_t s);
 void launch_gather_y(const float* y, const uint32_t* rows, long long n, float* out, cudaStream_t s);
 void launch_count_nonfinite(const float* X, long long n, int f, long long ldx, const float* y, unsigned long long* out /* [2], zeroed */, cudaStream_t s);
 

@@ -688,6 +688,19 @@ void launch_ingest_tile(const void* tile, int dtype, int colmajor, long long ld,
     else k_ingest_tile<float, false><<<grid, 256, 0, s>>>((const float*)tile, ld, rows, f, X, ldx, r0);
   }
 }
+// train rows per (feature, bin) of one fold, in the cell order of a node histogram ([group][bin][feature lane])
+static __global__ void __launch_bounds__(256) k_count_hist(const uint8_t* __restrict__ bins, int f, int fpad, long long ntrain, int* __restrict__ out) {
+  const long long total = ntrain * f;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / f;
+    const int c = (int)(i - r * f);
+    const int b = bins[r * fpad + c];
+    atomicAdd(&out[((c / kLanes) * kBins + b) * kLanes + (c % kLanes)], 1);
+  }
+}
+void launch_count_hist(const uint8_t* bins, int f, int fpad, long long ntrain, int* out /* zeroed */, cudaStream_t s) {
+  k_count_hist<<<148 * 8, 256, 0, s>>>(bins, f, fpad, ntrain, out);
+}
 void launch_gather_y(const float* y, const uint32_t* rows, long long n, float* out, cudaStream_t s) {
   int blocks = (int)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
   if (blocks < 1) blocks = 1;
