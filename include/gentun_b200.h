@@ -152,7 +152,8 @@ int gt_make_folds(int64_t n, int32_t nfold, uint32_t seed, int64_t* perm, int64_
  * __device__ array inside the library (about 2.2 MB per GPU, held until exit) -- no cudaMalloc, no
  * cudaFree, no allocating library call.  d_values [n] (device, the column in DMatrix row order),
  * d_cuts [GT_MAX_BIN] and d_ncuts [1] (device) are the caller's; work is enqueued on `stream`
- * (a cudaStream_t, NULL = default stream) and the call returns without synchronising.
+ * (a cudaStream_t, NULL = default stream) and the call returns without synchronising.  Only d_cuts[0 .. *d_ncuts)
+ * is written; the rest of the caller's GT_MAX_BIN floats is left as it was.
  * Limits: 1 <= n <= gt_column_cuts_noalloc_max_rows() (65536), else GT_ERR_ARG.  All calls share the
  * one scratch array: issue them on one stream, or otherwise keep them from overlapping on the GPU --
  * overlapping calls race.  The first call on each device looks the array's address up

@@ -25,3 +25,13 @@ for f, cls in ((50, False), (70, True)):
     print(f, cls, fit, rounds, flush=True)
     eng.close()
 print("done")
+
+# the shared-memory-resident regime (csrc/small.cu): team barriers, per-feature lists, early stopping, more
+# individuals than teams is not needed here (the queue is exercised by tests/test_gpu_small.py)
+x, y = make_dataset(3000, 9, seed=5)
+eng = Engine(x, y)
+fit, rounds = eng.evaluate([genes(max_depth=8, min_child_weight=0), genes(max_depth=5, subsample=0.7, colsample_bytree=0.6),
+                            genes(max_depth=3, eta=1.0)], nfold=3, num_boost_round=12, early_stopping_rounds=3)
+print("small", fit, rounds, eng.stats()["kernel_launches"], flush=True)
+eng.close()
+print("done small")
