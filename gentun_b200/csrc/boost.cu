@@ -370,12 +370,12 @@ enum FlushMode {
   kFlushAddWide       // node owned by this CTA, later flushes: add to what it stored before
 };
 template <int UNITS>
-__device__ __forceinline__ void hist_flush(const Wave& w, const JobParams& jp, int level, const HistItem& it, int cg, int* sh,
+__device__ __forceinline__ void hist_flush(const Wave& w, const JobParams& jp, int level, const HistItem& it, int g_first, int* sh,
                                            FlushMode mode, bool rezero) {
   constexpr int kThreads = UNITS == 2 ? 256 : 512;
   constexpr int kGroupsPerCta = UNITS / 2;
   HistEntry* slot = node_hist(w, jp, level, it.node);
-  const size_t c0 = (size_t)cg * kGroupsPerCta * (kBins * kLanes);   // first cell of this CTA's groups inside the node
+  const size_t c0 = (size_t)g_first * (kBins * kLanes);   // first cell of this CTA's groups inside the node
   for (int i = threadIdx.x; i < kGroupsPerCta * kBins * kLanes; i += kThreads) {
     const int gsel = i / (kBins * kLanes), cell = i % (kBins * kLanes);
     int* pg = sh + gsel * (2 * kBins * kLanes) + cell;
@@ -396,7 +396,7 @@ __device__ __forceinline__ void hist_flush(const Wave& w, const JobParams& jp, i
 }
 
 template <int UNITS>
-__global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 2 : 1) k_hist(Wave w, int level) {
+__global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 2 : 1) k_hist(Wave w, int level, int g0, int ncg) {
   constexpr int kThreads = UNITS == 2 ? 256 : 512;
   constexpr int kGroupsPerCta = UNITS / 2;
   constexpr uint32_t kStride = (kThreads / 32) * 32u;          // rows per CTA iteration
@@ -405,7 +405,7 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 2 : 1) k_
   // (all individuals of fold 0, then fold 1, ...).  CTAs are dispatched x-fastest, so the CTAs in flight at one time
   // are the SAME item index of many jobs of ONE fold: with row sets still near the identity they read the same bin
   // rows, which then come from L2 for all but the first of them (level-0 DRAM reads 9.0 -> 2.3 GB on the C3 shape).
-  const int ncg = w.groups / kGroupsPerCta;
+  // this launch covers the feature groups [g0, g0 + ncg * kGroupsPerCta) in ncg slices of kGroupsPerCta groups
   int j, item_idx, cg;
   if (level <= kJobFastestLevels) {
     const int lvl_jobs = (int)gridDim.x / ncg, lvl_inds = lvl_jobs / w.nfold;
@@ -419,6 +419,7 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 2 : 1) k_
   }
   const JobState& js = w.js[j];
   if (item_idx >= js.n_hist_items) return;
+  const int g_first = g0 + cg * kGroupsPerCta;
   const JobParams& jp = w.jp[j];
   const HistItem it = w.hitems[(size_t)j * w.hist_cap + item_idx];
   extern __shared__ int sh[];   // [group in CTA][g plane | h plane][bin][feature lane]
@@ -436,7 +437,7 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 2 : 1) k_
   const int rot = UNITS == 2 ? rslot : rslot * 2 + (unit >> 1);   // 16 distinct rotations per bank half
   const bool q1 = (rot >> 2) & 1, q2 = (rot >> 3) & 1;
   const int rb = (rot & 3) * 8;
-  const uint8_t* bins_unit = w.folds[jp.fold].bins + (size_t)cg * kGroupsPerCta * kLanes + unit * 16;
+  const uint8_t* bins_unit = w.folds[jp.fold].bins + (size_t)g_first * kLanes + unit * 16;
   const int2* gq = w.gq + (size_t)j * w.nt_stride;
   const int fpad = w.fpad;
   const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(sh);
@@ -503,7 +504,7 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 2 : 1) k_
       const bool must = __syncthreads_or((run_g >= lim_g || run_h >= lim_h) && !never_early);
 #ifdef GT_HIST_NO_LOOK
       if (must) {
-        hist_flush<UNITS>(w, jp, level, it, cg, sh, shared_node ? kFlushAtomic : stored ? kFlushAddWide : kFlushStoreWide, true);
+        hist_flush<UNITS>(w, jp, level, it, g_first, sh, shared_node ? kFlushAtomic : stored ? kFlushAddWide : kFlushStoreWide, true);
         stored = true;
         run_g = 0u; run_h = 0u;
         __syncthreads();
@@ -525,7 +526,7 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 2 : 1) k_
 #pragma unroll
         for (unsigned q = 0; q < kWarps; ++q) m = max(m, s_cellmax[q]);
         if (m >= 0x40000000u) {
-          hist_flush<UNITS>(w, jp, level, it, cg, sh, shared_node ? kFlushAtomic : stored ? kFlushAddWide : kFlushStoreWide, true);
+          hist_flush<UNITS>(w, jp, level, it, g_first, sh, shared_node ? kFlushAtomic : stored ? kFlushAddWide : kFlushStoreWide, true);
           stored = true;
           m = 0u;
         }
@@ -538,12 +539,12 @@ __global__ void __launch_bounds__(UNITS == 2 ? 256 : 512, UNITS == 2 ? 2 : 1) k_
     }
   }
   // the node's exact sum of |g_q| decides the cell format of its children (child_narrow)
-  if (cg == 0) {
+  if (g_first == 0) {
     const unsigned warp_abs = __reduce_add_sync(0xffffffffu, abs_rows + acc_g);
     if (lane == 0 && warp_abs) atomicAdd(&node.absG, (unsigned long long)warp_abs);
   }
   __syncthreads();
-  hist_flush<UNITS>(w, jp, level, it, cg, sh,
+  hist_flush<UNITS>(w, jp, level, it, g_first, sh,
                     shared_node ? kFlushAtomic : never_early ? kFlushStoreNarrow : stored ? kFlushAddWide : kFlushStoreWide, false);
 }
 
@@ -1685,12 +1686,22 @@ int launch_hist(const Wave& w, int level, cudaStream_t s) {   // returns the num
   int cap = hist_items_bound(w, level);
   const int jobs = w.lvl_jobs[level];
   const bool job_fastest = level <= kJobFastestLevels;
-  if (w.groups % 2 == 0) {
-    const int ncg = w.groups / 2;
-    k_hist<4><<<job_fastest ? dim3(jobs * ncg, cap) : dim3(cap * ncg, jobs), 512, 2 * kHistSmem, s>>>(w, level);
-  } else {
-    k_hist<2><<<job_fastest ? dim3(jobs * w.groups, cap) : dim3(cap * w.groups, jobs), 256, kHistSmem, s>>>(w, level);
+  // Two kernels: a 128-KiB CTA that takes a pair of feature groups (the whole 64-byte line of a 50-feature row; one CTA
+  // per SM) and a 64-KiB CTA that takes one group (two CTAs per SM, whose fixed phases overlap).  Measured on B200
+  // (profiles/r02_hist_experiments.md): pair CTAs win for 2 and 4 groups; for 7 groups seven single-group CTAs beat
+  // three pairs plus a single, so an odd count goes to the single-group kernel throughout.
+  int launched = 0;
+  const int pairs = w.groups % 2 == 0 ? w.groups / 2 : 0;
+  const int singles = w.groups - 2 * pairs;
+  if (pairs) {
+    k_hist<4><<<job_fastest ? dim3(jobs * pairs, cap) : dim3(cap * pairs, jobs), 512, 2 * kHistSmem, s>>>(w, level, 0, pairs);
+    ++launched;
   }
+  if (singles) {
+    k_hist<2><<<job_fastest ? dim3(jobs * singles, cap) : dim3(cap * singles, jobs), 256, kHistSmem, s>>>(w, level, 2 * pairs, singles);
+    ++launched;
+  }
+  return launched;
   return 1;
 }
 int launch_scan(const Wave& w, int level, cudaStream_t s) {   // returns the number of kernels launched

@@ -126,7 +126,6 @@ __global__ void __launch_bounds__(kST, 2) k_small_cv(SmallWave w) {
   float* s_leaf = reinterpret_cast<float*>(s_walk + kNodeCap);
   int* s_scr = reinterpret_cast<int*>(s_leaf + kNodeCap);     // 256 ints of scratch
   __shared__ uint32_t s_tmask[kMaskWords], s_lmask[kMaskWords], s_in[kMaskWords];
-  __shared__ uint16_t s_firstbin[kST + 1];
   __shared__ double s_dm[2][8], s_mpart[8];
   __shared__ float s_fm[2][kST / 32];
   __shared__ long long s_ll[2][kST / 32];
@@ -140,7 +139,6 @@ __global__ void __launch_bounds__(kST, 2) k_small_cv(SmallWave w) {
   unsigned* bar = w.team_bar + team;
   const FoldDev fd = w.folds[fold];
   const int ntrain = (int)fd.ntrain, n = w.n, fpad = w.fpad, F = w.f;
-  const int C = (ntrain + kST - 1) / kST;                  // list elements per thread (contiguous chunk)
   Node* nodes = w.nodes + (size_t)blockIdx.x * kNodeCap;
   TreeNode* tree = w.tree + (size_t)blockIdx.x * kNodeCap;
   uint32_t* lists = w.lists + (size_t)blockIdx.x * 2 * F * w.nt_stride;
