@@ -14,6 +14,8 @@
 #include <memory>
 #include <mutex>
 #include <string>
+#include <thread>
+#include <utility>
 #include <vector>
 
 #include "../../include/gentun_b200.h"
@@ -771,13 +773,30 @@ int ingest_matrix(gt_engine* e, const HostMatrix& m) {
     if (t >= 2 && cudaEventSynchronize(done[b]) != cudaSuccess) { rc = fail(GT_ERR_CUDA, "staging event failed"); break; }
     unsigned char* pin = (unsigned char*)g_stage.buf[b];
     size_t bytes;
+    // the host-side gather into the pinned tile is the slow leg for large matrices (one core copies ~6 GB/s): a few
+    // threads share it (pieces of 64 KB at least)
+    std::vector<std::pair<const unsigned char*, unsigned char*>> piece_ptr;
+    std::vector<size_t> piece_len;
+    auto add_piece = [&](const unsigned char* src, unsigned char* dst, size_t len) {
+      const size_t step = std::max<size_t>(64u << 10, (len + 7) / 8);
+      for (size_t o = 0; o < len; o += step) { piece_ptr.emplace_back(src + o, dst + o); piece_len.push_back(std::min(step, len - o)); }
+    };
     if (colmajor) {   // tile = [f][rows]
       for (int c = 0; c < f; ++c)
-        memcpy(pin + (size_t)c * rows * esz, (const unsigned char*)m.p + ((size_t)c * m.col_stride + (size_t)r0) * esz, (size_t)rows * esz);
+        add_piece((const unsigned char*)m.p + ((size_t)c * m.col_stride + (size_t)r0) * esz, pin + (size_t)c * rows * esz, (size_t)rows * esz);
       bytes = (size_t)f * rows * esz;
     } else {          // tile = [rows][row_stride]
       bytes = ((size_t)(rows - 1) * m.row_stride + f) * esz;
-      memcpy(pin, (const unsigned char*)m.p + (size_t)r0 * m.row_stride * esz, bytes);
+      add_piece((const unsigned char*)m.p + (size_t)r0 * m.row_stride * esz, pin, bytes);
+    }
+    {
+      const unsigned hw = std::thread::hardware_concurrency();
+      const int n_thr = (int)std::max(1u, std::min(std::min(8u, hw ? hw / 2 : 1u), (unsigned)(bytes >> 20)));   // tiles below a few MB: one thread
+      auto work = [&](int t) { for (size_t q = (size_t)t; q < piece_ptr.size(); q += (size_t)n_thr) memcpy(piece_ptr[q].second, piece_ptr[q].first, piece_len[q]); };
+      std::vector<std::thread> pool;
+      for (int t = 1; t < n_thr; ++t) pool.emplace_back(work, t);
+      work(0);
+      for (auto& th : pool) th.join();
     }
     cudaError_t ce = cudaMemcpyAsync(d_tile[b].p, pin, bytes, cudaMemcpyHostToDevice, e->stream);
     if (ce != cudaSuccess) { rc = fail(GT_ERR_CUDA, "H2D of a staged tile failed: %s", cudaGetErrorString(ce)); break; }
