@@ -121,12 +121,36 @@ def test_hundred_round_drift_against_frozen_oracle():
         assert rounds[0] == len(want)
 
 
+@pytest.mark.parametrize("n,f,nfold,cls", [(2_000_000, 100, 3, True), (1_000_000, 200, 5, False)])
+def test_c4_c5_feature_widths_parity_with_oracle(n, f, nfold, cls):
+    """The other two streaming shapes against the oracle at a size it finishes in seconds: 100 features (four groups, pair
+    CTAs, logistic / logloss as in C4) and 200 features (seven groups, single-group CTAs, as in C5); every round's CV
+    mean within 1e-4 for a deep and a regularised individual."""
+    from gentun_b200.engine import Engine
+    from oracle import orc
+    x, y = make_dataset(n, f, seed=1000 + f, classification=cls)
+    eng = Engine(x, y)
+    ctx = orc.Context(x, y, nfold, nthread=orc.host_cores())
+    pop = seeded_population_genes(64)
+    plain = [g for g in pop if g["subsample"] == 1.0 and g["colsample_bytree"] == 1.0 and g["colsample_bylevel"] == 1.0]
+    gs = [max(plain, key=lambda g: g["max_depth"]), next(g for g in plain if g["max_delta_step"] != 0 and g["max_depth"] <= 6)]
+    params = dict(nfold=nfold, num_boost_round=3)
+    if cls:
+        params.update(objective="binary:logistic", eval_metric="logloss")
+    fit, rounds, extra = eng.evaluate(gs, trace=True, **params)
+    for i, g in enumerate(gs):
+        want = ctx.cv(g, orc.make_opts(nthread=orc.host_cores(), **params), trace=True)
+        np.testing.assert_allclose(extra["trace"][i, :3], want["trace"], rtol=1e-4)      # north_star: 1e-4 relative
+    eng.close()
+    ctx.close()
+
+
 def test_c3_shape_1m_by_50_regression():
     _properties(1_000_000, 50, 5, False)
 
 
 def test_c4_shape_logistic_100_features():
-    _properties(2_000_000, 100, 3, True)       # C4's 10M rows need 4 GB of host data; same kernels, same groups
+    _properties(10_000_000, 100, 3, True, rounds=3, n_ind=2)       # C4 at its full 10M rows (4 GB of host data)
 
 
 def test_c5_shape_200_features():
