@@ -6,6 +6,6 @@ from tests.test_gpu_parity import genes
 df = pd.read_csv('tests/data/winequality-white.csv', delimiter=';')
 x = np.ascontiguousarray(df.drop(['quality'], axis=1).values, dtype=np.float32); y = np.ascontiguousarray(df['quality'].values, dtype=np.float32)
 eng = Engine(x, y); eng.prepare(3)
-gs = [genes(max_depth=6, eta=0.01, gamma=1e-4 * i) for i in range(int(os.environ.get('COPIES', '1')))]
+gs = [genes(max_depth=int(os.environ.get('DEPTH', '6')), eta=0.01, min_child_weight=int(os.environ.get('MCW', '1')), gamma=1e-4 * i) for i in range(int(os.environ.get('COPIES', '1')))]
 eng.evaluate(gs, nfold=3, num_boost_round=int(os.environ.get('R', '30')), early_stopping_rounds=0)
 print(eng.stats()['eval_ms'])
