@@ -38,6 +38,8 @@ __device__ unsigned long long g_small_prof[16];
 constexpr int kST = kSmallThreads;
 constexpr int kSlots = 1 << (kMaxDepth - 1);       // nodes of the deepest evaluated level
 constexpr uint16_t kNoSlot = 0xffffu;
+constexpr int kBatch = 32;                          // features whose sweeps run side by side
+constexpr int kMaxChunks = (kSmallMaxTrain + 127) / 128;   // 128-element chunks of a list
 static_assert(kSlots <= kST, "one thread per node slot");
 static_assert(kSmallMaxTrain <= 8 * kST, "eight list elements per thread");
 
@@ -115,7 +117,7 @@ int small_smem_bytes(int n, int nt_stride) {
 
 namespace {
 
-__global__ void __launch_bounds__(kST, 2) k_small_cv(SmallWave w) {
+__global__ void __launch_bounds__(kST, 1) k_small_cv(SmallWave w) {
   extern __shared__ __align__(16) unsigned char s_raw[];
   SlotArrays& S = *reinterpret_cast<SlotArrays*>(s_raw);
   float* s_pred = reinterpret_cast<float*>(s_raw + sizeof(SlotArrays));
@@ -126,7 +128,11 @@ __global__ void __launch_bounds__(kST, 2) k_small_cv(SmallWave w) {
   float* s_leaf = reinterpret_cast<float*>(s_walk + kNodeCap);
   int* s_scr = reinterpret_cast<int*>(s_leaf + kNodeCap);     // 256 ints of scratch
   __shared__ uint32_t s_tmask[kMaskWords], s_lmask[kMaskWords], s_in[kMaskWords];
-  __shared__ double s_dm[2][8], s_mpart[8];
+  __shared__ double s_dm[kST / 256][8], s_mpart[8];
+  __shared__ int2 s_cv[kBatch][kMaxChunks];            // look-back: running sums at the end of (feature in batch, chunk)
+  __shared__ unsigned s_cf[kBatch][kMaxChunks];        // ... valid when it holds the sweep's epoch
+  __shared__ uint16_t s_feats[256];                    // the sweep's features
+  unsigned epoch = 0u;
   __shared__ float s_fm[2][kST / 32];
   __shared__ long long s_ll[2][kST / 32];
   __shared__ int s_i[4];
@@ -145,6 +151,8 @@ __global__ void __launch_bounds__(kST, 2) k_small_cv(SmallWave w) {
   const uint32_t* base_lists = w.base_lists + (size_t)fold * F * w.nt_stride;
   const int pred_chunks = (n + kPredRows - 1) / kPredRows;
   int parity = 0;
+  for (int i = tid; i < kBatch * kMaxChunks; i += kST) (&s_cf[0][0])[i] = 0u;     // no entry carries an epoch yet (epochs start at 1)
+  __syncthreads();
 #ifdef GT_SMALL_PROF
   long long prof_t = clock64();
 #endif
@@ -238,7 +246,7 @@ __global__ void __launch_bounds__(kST, 2) k_small_cv(SmallWave w) {
       int m = 1;                                  // nodes of the level (slots)
       const uint32_t* cur = base_lists;           // level 0 reads the fold's base lists; later levels ping-pong
       int pp = 0;
-      const int n_iters = (ntrain + 127) / 128;
+      const int n_chunks = (ntrain + 127) / 128;
       for (int level = 0; level < jp.max_depth && m > 0; ++level) {
         // feature sets (k_plan_hist): colsample_bytree once per tree, colsample_bylevel at every level
         if (level == 0) {
@@ -270,43 +278,70 @@ __global__ void __launch_bounds__(kST, 2) k_small_cv(SmallWave w) {
         PROF_MARK(2);
         // ---- split search.  The prefix sums of a list run over ALL its rows; what lies in front of a node's segment
         // (the same rows for every feature, hence the same sums) is noted when the sweep enters the segment.
-        for (int f = wid; f < F; f += kST / 32) {
-          if (!((s_lmask[f >> 5] >> (f & 31)) & 1u)) continue;            // warp-uniform
-          const uint4* lst4 = reinterpret_cast<const uint4*>(cur + (size_t)f * w.nt_stride);
-          int carry_g = 0, carry_h = 0;
-          uint4 q_next = lane * 4 < ntrain ? lst4[lane] : make_uint4(0u, 0u, 0u, 0u);
-          for (int it = 0; it < n_iters; ++it) {
-            // a lane takes 4 consecutive elements: its own running sums first, one warp scan per 128 elements
-            const int i0 = it * 128 + lane * 4;
-            const uint4 q = q_next;
-            q_next = (i0 + 128 < ntrain) ? lst4[(it + 1) * 32 + lane] : make_uint4(0u, 0u, 0u, 0u);   // on its way while this one is worked
+        // prefix sums in front of every node's segment: rows of finished nodes count as zero in the sweeps, and the nodes of a
+        // level lie in the lists in slot order, so it is the sum of the earlier nodes' totals
+        {
+          int og, oh;
+          const int gt = tid < m ? S.Gt[tid] : 0, ht = tid < m ? S.Ht[tid] : 0;
+          block_excl_scan2(gt, ht, og, oh, s_scr);
+          if (tid < m) { S.baseG[tid] = og; S.baseH[tid] = oh; }
+        }
+        // the level's features, compacted
+        if (wid == 0) {
+          int cnt = 0;
+          for (int f0 = 0; f0 < F; f0 += 32) {
+            const int f = f0 + lane;
+            const bool on = f < F && ((s_lmask[f >> 5] >> (f & 31)) & 1u);
+            const unsigned bal = __ballot_sync(0xffffffffu, on);
+            if (on) s_feats[cnt + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)f;
+            cnt += __popc(bal);
+          }
+          if (lane == 0) s_i[2] = cnt;
+        }
+        __syncthreads();
+        const int n_feats = s_i[2];
+        // A list is cut into chunks of 128 elements; (chunk, feature) tasks are dealt to the warps chunk-major, so every warp
+        // of the CTA works whatever the number of features, and a task's running sums come from its predecessor chunk through
+        // shared memory (look-back: the predecessor always started earlier, possibly in this very warp).
+        for (int fb = 0; fb < n_feats; fb += kBatch) {
+          const int nfb = min(kBatch, n_feats - fb);
+          ++epoch;
+          for (int t = wid; t < n_chunks * nfb; t += kST / 32) {
+            const int chunk = t / nfb, fi = t % nfb;
+            const int f = s_feats[fb + fi];
+            const uint32_t* lst = cur + (size_t)f * w.nt_stride;
+            const int i0 = chunk * 128 + lane * 4;
+            const uint4 q = i0 < ntrain ? reinterpret_cast<const uint4*>(lst)[chunk * 32 + lane] : make_uint4(0u, 0u, 0u, 0u);
+            const uint32_t first_next = (lane == 31 && (chunk + 1) * 128 < ntrain) ? lst[(chunk + 1) * 128] : 0u;
             const uint32_t e[4] = {q.x, q.y, q.z, q.w};
             int pg[4], ph[4];
             uint16_t sl[4];
             int tg = 0, th = 0;
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-              const bool have = i0 + k < ntrain;
               const int row = (int)(e[k] & 0xffffu);
-              const int2 gh = have ? s_gq[row] : make_int2(0, 0);
-              sl[k] = have ? s_pos[row] : kNoSlot;
+              sl[k] = (i0 + k < ntrain) ? s_pos[row] : kNoSlot;
+              const int2 gh = sl[k] != kNoSlot ? s_gq[row] : make_int2(0, 0);
               tg += gh.x; th += gh.y;
               pg[k] = tg; ph[k] = th;
             }
-            const int og = warp_incl_scan(tg) - tg + carry_g, oh = warp_incl_scan(th) - th + carry_h;
-            carry_g = __shfl_sync(0xffffffffu, og + tg, 31); carry_h = __shfl_sync(0xffffffffu, oh + th, 31);
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              pg[k] += og; ph[k] += oh;
-              if (sl[k] != kNoSlot && i0 + k == S.beg[sl[k]]) {
-                const int2 gh = s_gq[e[k] & 0xffffu];
-                S.baseG[sl[k]] = pg[k] - gh.x; S.baseH[sl[k]] = ph[k] - gh.y;
+            const int ig = warp_incl_scan(tg), ih = warp_incl_scan(th);
+            int cg = 0, ch = 0;
+            if (lane == 31) {
+              if (chunk > 0) {
+                while (*reinterpret_cast<volatile unsigned*>(&s_cf[fi][chunk - 1]) != epoch) {}
+                cg = *reinterpret_cast<volatile int*>(&s_cv[fi][chunk - 1].x);
+                ch = *reinterpret_cast<volatile int*>(&s_cv[fi][chunk - 1].y);
               }
+              *reinterpret_cast<volatile int*>(&s_cv[fi][chunk].x) = cg + ig;
+              *reinterpret_cast<volatile int*>(&s_cv[fi][chunk].y) = ch + ih;
+              __threadfence_block();
+              *reinterpret_cast<volatile unsigned*>(&s_cf[fi][chunk]) = epoch;
             }
-            __syncwarp();
+            cg = __shfl_sync(0xffffffffu, cg, 31); ch = __shfl_sync(0xffffffffu, ch, 31);
+            const int og = cg + ig - tg, oh = ch + ih - th;
             uint32_t nb_lane = __shfl_down_sync(0xffffffffu, e[0] >> 16, 1);
-            const uint32_t nb_iter = __shfl_sync(0xffffffffu, q_next.x, 0) >> 16;
-            if (lane == 31) nb_lane = nb_iter;
+            if (lane == 31) nb_lane = first_next >> 16;
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
               const uint32_t bin = e[k] >> 16;
@@ -314,7 +349,7 @@ __global__ void __launch_bounds__(kST, 2) k_small_cv(SmallWave w) {
               const uint16_t slk = sl[k];
               // a candidate: the last row of a run of equal bins that is not the node's last row
               if (slk != kNoSlot && i0 + k + 1 < S.end[slk] && nb != bin) {
-                const int GL = pg[k] - S.baseG[slk], HL = ph[k] - S.baseH[slk];
+                const int GL = og + pg[k] - S.baseG[slk], HL = oh + ph[k] - S.baseH[slk];
                 const int Ht = S.Ht[slk];
                 if (HL >= hmin32 && Ht - HL >= hmin32) {
                   // stage 1: fp32 estimate; stage 2: exact gain (reference expression order) if the estimate is within
@@ -339,8 +374,8 @@ __global__ void __launch_bounds__(kST, 2) k_small_cv(SmallWave w) {
               }
             }
           }
+          __syncthreads();
         }
-        __syncthreads();
 
         PROF_MARK(3);
         // ---- the winning candidate of every node: which rows go left, and their sums (GL, HL, count)
@@ -411,16 +446,35 @@ __global__ void __launch_bounds__(kST, 2) k_small_cv(SmallWave w) {
         // ---- stable partition of every live feature's list (partition_builder.h), node by node in place; a warp per
         // feature again.  Lefts in front of a segment: noted on entering it, like the sums above.
         uint32_t* nxt = lists + (size_t)pp * F * w.nt_stride;
-        for (int f = wid; f < F; f += kST / 32) {
-          if (!((s_tmask[f >> 5] >> (f & 31)) & 1u)) continue;            // features outside the tree's set are never read again
-          const uint4* lst4 = reinterpret_cast<const uint4*>(cur + (size_t)f * w.nt_stride);
-          uint32_t* out = nxt + (size_t)f * w.nt_stride;
-          int carry = 0;
-          uint4 q_next = lane * 4 < ntrain ? lst4[lane] : make_uint4(0u, 0u, 0u, 0u);
-          for (int it = 0; it < n_iters; ++it) {
-            const int i0 = it * 128 + lane * 4;
-            const uint4 q = q_next;
-            q_next = (i0 + 128 < ntrain) ? lst4[(it + 1) * 32 + lane] : make_uint4(0u, 0u, 0u, 0u);
+        {   // lefts in front of every partitioned node's segment: the earlier partitioned nodes' left counts
+          int ol, dummy;
+          const int tl = (tid < m && S.sfeat[tid] >= 0) ? S.totL[tid] : 0;
+          block_excl_scan2(tl, 0, ol, dummy, s_scr);
+          if (tid < m) S.baseL[tid] = ol;
+        }
+        if (wid == 0) {     // the tree's features (features outside its set are never read again)
+          int cnt = 0;
+          for (int f0 = 0; f0 < F; f0 += 32) {
+            const int f = f0 + lane;
+            const bool on = f < F && ((s_tmask[f >> 5] >> (f & 31)) & 1u);
+            const unsigned bal = __ballot_sync(0xffffffffu, on);
+            if (on) s_feats[cnt + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)f;
+            cnt += __popc(bal);
+          }
+          if (lane == 0) s_i[2] = cnt;
+        }
+        __syncthreads();
+        const int n_pfeats = s_i[2];
+        for (int fb = 0; fb < n_pfeats; fb += kBatch) {
+          const int nfb = min(kBatch, n_pfeats - fb);
+          ++epoch;
+          for (int t = wid; t < n_chunks * nfb; t += kST / 32) {
+            const int chunk = t / nfb, fi = t % nfb;
+            const int f = s_feats[fb + fi];
+            const uint32_t* lst = cur + (size_t)f * w.nt_stride;
+            uint32_t* out = nxt + (size_t)f * w.nt_stride;
+            const int i0 = chunk * 128 + lane * 4;
+            const uint4 q = i0 < ntrain ? reinterpret_cast<const uint4*>(lst)[chunk * 32 + lane] : make_uint4(0u, 0u, 0u, 0u);
             const uint32_t e[4] = {q.x, q.y, q.z, q.w};
             int pl[4], lk[4];
             uint16_t sl[4];
@@ -434,28 +488,33 @@ __global__ void __launch_bounds__(kST, 2) k_small_cv(SmallWave w) {
               pl[k] = tl;                                                      // exclusive, lane-local
               tl += lk[k];
             }
-            const int ol = warp_incl_scan(tl) - tl + carry;
-            carry = __shfl_sync(0xffffffffu, ol + tl, 31);
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              pl[k] += ol;
-              if (sl[k] != kNoSlot && i0 + k == S.beg[sl[k]]) S.baseL[sl[k]] = pl[k];
+            const int il = warp_incl_scan(tl);
+            int cl = 0;
+            if (lane == 31) {
+              if (chunk > 0) {
+                while (*reinterpret_cast<volatile unsigned*>(&s_cf[fi][chunk - 1]) != epoch) {}
+                cl = *reinterpret_cast<volatile int*>(&s_cv[fi][chunk - 1].x);
+              }
+              *reinterpret_cast<volatile int*>(&s_cv[fi][chunk].x) = cl + il;
+              __threadfence_block();
+              *reinterpret_cast<volatile unsigned*>(&s_cf[fi][chunk]) = epoch;
             }
-            __syncwarp();
+            cl = __shfl_sync(0xffffffffu, cl, 31);
+            const int ol = cl + il - tl;
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
               if (i0 + k < ntrain) {
                 int dest = i0 + k;
                 if (sl[k] != kNoSlot) {
-                  const int beg = S.beg[sl[k]], rankL = pl[k] - S.baseL[sl[k]];
+                  const int beg = S.beg[sl[k]], rankL = ol + pl[k] - S.baseL[sl[k]];
                   dest = lk[k] ? beg + rankL : beg + S.totL[sl[k]] + (i0 + k - beg - rankL);
                 }
                 out[dest] = e[k];
               }
             }
           }
+          __syncthreads();
         }
-        __syncthreads();
         PROF_MARK(6);
         // ---- next level's nodes: the open children, in node order
         {
