@@ -112,6 +112,7 @@ int small_smem_bytes(int n, int nt_stride) {
   b += (size_t)nt_stride;             // goes-left flags
   b += (size_t)kNodeCap * 8;          // tree: walk words + leaf values
   b += 1024;                          // scratch
+  b += (size_t)(kSmallThreads / 32) * 128 * 16;   // per-warp candidate lists
   return (int)((b + 15) / 16 * 16);
 }
 
@@ -127,6 +128,7 @@ __global__ void __launch_bounds__(kST, 1) k_small_cv(SmallWave w) {
   uint32_t* s_walk = reinterpret_cast<uint32_t*>(s_left + w.nt_stride);
   float* s_leaf = reinterpret_cast<float*>(s_walk + kNodeCap);
   int* s_scr = reinterpret_cast<int*>(s_leaf + kNodeCap);     // 256 ints of scratch
+  int4* s_stage = reinterpret_cast<int4*>(s_scr + 256);        // per warp: the candidates of one chunk, dense
   __shared__ uint32_t s_tmask[kMaskWords], s_lmask[kMaskWords], s_in[kMaskWords];
   __shared__ double s_dm[kST / 256][8], s_mpart[8];
   __shared__ int2 s_cv[kBatch][kMaxChunks];            // look-back: running sums at the end of (feature in batch, chunk)
@@ -342,37 +344,49 @@ __global__ void __launch_bounds__(kST, 1) k_small_cv(SmallWave w) {
             const int og = cg + ig - tg, oh = ch + ih - th;
             uint32_t nb_lane = __shfl_down_sync(0xffffffffu, e[0] >> 16, 1);
             if (lane == 31) nb_lane = first_next >> 16;
+            // Candidates (the last row of a run of equal bins that is not its node's last row) are a minority of the
+            // elements and scattered over the lanes, so they are first gathered into a dense per-warp list in shared
+            // memory; the arithmetic below then runs with every lane busy.
+            int4* stage = s_stage + wid * 128;
+            int n_cand = 0;
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
               const uint32_t bin = e[k] >> 16;
               const uint32_t nb = k < 3 ? (e[(k + 1) & 3] >> 16) : nb_lane;
               const uint16_t slk = sl[k];
-              // a candidate: the last row of a run of equal bins that is not the node's last row
-              if (slk != kNoSlot && i0 + k + 1 < S.end[slk] && nb != bin) {
-                const int GL = og + pg[k] - S.baseG[slk], HL = oh + ph[k] - S.baseH[slk];
-                const int Ht = S.Ht[slk];
-                if (HL >= hmin32 && Ht - HL >= hmin32) {
-                  // stage 1: fp32 estimate; stage 2: exact gain (reference expression order) if the estimate is within
-                  // its own error of the best estimate seen so far for the node -- a bound that only rises, so nothing
-                  // that could win is skipped
-                  const float Gt_f = (float)S.Gt[slk] * isg, Ht_f = (float)Ht * ish;
-                  const float glf = (float)GL * isg, hlf = (float)HL * ish;
-                  const float v = mds_on ? split_est<true>(gk, glf, hlf, Gt_f - glf, Ht_f - hlf)
-                                         : split_est<false>(gk, glf, hlf, Gt_f - glf, Ht_f - hlf);
-                  PROF_COUNT(12);
-                  const float est = fmaxf(v, 0.0f);
-                  const float seen = __uint_as_float(S.amax[slk]);             // may be stale: any lower bound of the final maximum will do
-                  if (est > seen) atomicMax(&S.amax[slk], __float_as_uint(est));
-                  const float amax = fmaxf(seen, est), rg = S.root_gain[slk];
-                  const float margin = 3.2e-5f * (amax + fabsf(rg)) + 1e-12f;
-                  if (est >= fmaxf(amax, rg) - 2.0f * margin) {
-                    PROF_COUNT(13);
-                    const unsigned long long key = exact_key(jp, S.Gt[slk], Ht, rg, GL, HL, f, (int)bin, inv_sg, inv_sh);
-                    if (key) atomicMax(&S.key[slk], key);
-                  }
+              const bool cand = slk != kNoSlot && i0 + k + 1 < S.end[slk] && nb != bin;
+              const unsigned bal = __ballot_sync(0xffffffffu, cand);
+              if (cand) stage[n_cand + __popc(bal & ((1u << lane) - 1u))] = make_int4(og + pg[k], oh + ph[k], (int)slk, (int)bin);
+              n_cand += __popc(bal);
+            }
+            __syncwarp();
+            for (int c = lane; c < n_cand; c += 32) {
+              const int4 rec = stage[c];
+              const int slk = rec.z;
+              const int GL = rec.x - S.baseG[slk], HL = rec.y - S.baseH[slk];
+              const int Ht = S.Ht[slk];
+              if (HL >= hmin32 && Ht - HL >= hmin32) {
+                // stage 1: fp32 estimate; stage 2: exact gain (reference expression order) if the estimate is within
+                // its own error of the best estimate seen so far for the node -- a bound that only rises, so nothing
+                // that could win is skipped
+                const float Gt_f = (float)S.Gt[slk] * isg, Ht_f = (float)Ht * ish;
+                const float glf = (float)GL * isg, hlf = (float)HL * ish;
+                const float v = mds_on ? split_est<true>(gk, glf, hlf, Gt_f - glf, Ht_f - hlf)
+                                       : split_est<false>(gk, glf, hlf, Gt_f - glf, Ht_f - hlf);
+                PROF_COUNT(12);
+                const float est = fmaxf(v, 0.0f);
+                const float seen = __uint_as_float(S.amax[slk]);             // may be stale: any lower bound of the final maximum will do
+                if (est > seen) atomicMax(&S.amax[slk], __float_as_uint(est));
+                const float amax = fmaxf(seen, est), rg = S.root_gain[slk];
+                const float margin = 3.2e-5f * (amax + fabsf(rg)) + 1e-12f;
+                if (est >= fmaxf(amax, rg) - 2.0f * margin) {
+                  PROF_COUNT(13);
+                  const unsigned long long key = exact_key(jp, S.Gt[slk], Ht, rg, GL, HL, f, rec.w, inv_sg, inv_sh);
+                  if (key) atomicMax(&S.key[slk], key);
                 }
               }
             }
+            __syncwarp();     // the list is rewritten by the warp's next task
           }
           __syncthreads();
         }
