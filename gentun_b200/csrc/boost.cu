@@ -324,7 +324,7 @@ __device__ __forceinline__ void hist_load(HistStage<UNITS>& st, uint32_t myrow, 
     // rows past the end of the item read row 0 and add a zero gradient: no predicate in the hot loop
     const bool ok = r != 0xffffffffu;
     const uint32_t a = ok ? r : 0u;
-    st.b[sb] = ld_stream(reinterpret_cast<const uint4*>(bins_unit + (size_t)a * fpad));
+    st.b[sb] = ld_stream(reinterpret_cast<const uint4*>(bins_unit + (unsigned long long)a * (unsigned)fpad));   // u32 x u32 + u64: one IMAD.WIDE
   }
   // one coalesced gather for the warp's 32 rows (each lane its own row) instead of one per sub-batch
   st.gv = myrow != 0xffffffffu ? gq[myrow] : make_int2(0, 0);
