@@ -104,31 +104,40 @@ __device__ __forceinline__ void team_barrier(unsigned* bar, unsigned& target, in
 
 }  // namespace
 
+namespace {
+constexpr size_t kTrainCap = (kSmallMaxTrain + 32) / 32 * 32;
+constexpr size_t kOffPred = (sizeof(SlotArrays) + 15) / 16 * 16;
+constexpr size_t kOffGq = kOffPred + (size_t)kSmallMaxRows * 4;
+constexpr size_t kOffPos = kOffGq + kTrainCap * 8;
+constexpr size_t kOffLeft = kOffPos + kTrainCap * 2;
+constexpr size_t kOffWalk = kOffLeft + kTrainCap;
+constexpr size_t kOffLeaf = kOffWalk + (size_t)kNodeCap * 4;
+constexpr size_t kOffScr = kOffLeaf + (size_t)kNodeCap * 4;
+constexpr size_t kOffStage = kOffScr + 1024;
+constexpr size_t kSmallSmem = kOffStage + (size_t)(kSmallThreads / 32) * 128 * 16;
+static_assert(kSmallSmem + 16 * 1024 <= 227 * 1024, "dynamic + static shared memory of k_small_cv must fit one SM");
+}  // namespace
+
 int small_smem_bytes(int n, int nt_stride) {
-  size_t b = sizeof(SlotArrays);
-  b += (size_t)((n + 3) & ~3) * 4;    // predictions
-  b += (size_t)nt_stride * 8;         // quantised gradient pairs
-  b += (size_t)nt_stride * 2;         // node slot of every train row
-  b += (size_t)nt_stride;             // goes-left flags
-  b += (size_t)kNodeCap * 8;          // tree: walk words + leaf values
-  b += 1024;                          // scratch
-  b += (size_t)(kSmallThreads / 32) * 128 * 16;   // per-warp candidate lists
-  return (int)((b + 15) / 16 * 16);
+  (void)n; (void)nt_stride;
+  return (int)kSmallSmem;
 }
 
 namespace {
 
 __global__ void __launch_bounds__(kST, 1) k_small_cv(SmallWave w) {
   extern __shared__ __align__(16) unsigned char s_raw[];
+  // fixed offsets (the maxima of the regime, not this data set's sizes): every array's address is a compile-time constant
+  // off the one base, which the 64-register budget would otherwise make the compiler recompute at every use
   SlotArrays& S = *reinterpret_cast<SlotArrays*>(s_raw);
-  float* s_pred = reinterpret_cast<float*>(s_raw + sizeof(SlotArrays));
-  int2* s_gq = reinterpret_cast<int2*>(s_pred + ((w.n + 3) & ~3));   // 16-byte aligned whatever n is
-  uint16_t* s_pos = reinterpret_cast<uint16_t*>(s_gq + w.nt_stride);
-  uint8_t* s_left = reinterpret_cast<uint8_t*>(s_pos + w.nt_stride);
-  uint32_t* s_walk = reinterpret_cast<uint32_t*>(s_left + w.nt_stride);
-  float* s_leaf = reinterpret_cast<float*>(s_walk + kNodeCap);
-  int* s_scr = reinterpret_cast<int*>(s_leaf + kNodeCap);     // 256 ints of scratch
-  int4* s_stage = reinterpret_cast<int4*>(s_scr + 256);        // per warp: the candidates of one chunk, dense
+  float* s_pred = reinterpret_cast<float*>(s_raw + kOffPred);
+  int2* s_gq = reinterpret_cast<int2*>(s_raw + kOffGq);
+  uint16_t* s_pos = reinterpret_cast<uint16_t*>(s_raw + kOffPos);
+  uint8_t* s_left = s_raw + kOffLeft;
+  uint32_t* s_walk = reinterpret_cast<uint32_t*>(s_raw + kOffWalk);
+  float* s_leaf = reinterpret_cast<float*>(s_raw + kOffLeaf);
+  int* s_scr = reinterpret_cast<int*>(s_raw + kOffScr);         // 256 ints of scratch
+  int4* s_stage = reinterpret_cast<int4*>(s_raw + kOffStage);   // per warp: the candidates of one chunk, dense
   __shared__ uint32_t s_tmask[kMaskWords], s_lmask[kMaskWords], s_in[kMaskWords];
   __shared__ double s_dm[kST / 256][8], s_mpart[8];
   __shared__ int2 s_cv[kBatch][kMaxChunks];            // look-back: running sums at the end of (feature in batch, chunk)
@@ -307,9 +316,10 @@ __global__ void __launch_bounds__(kST, 1) k_small_cv(SmallWave w) {
         // shared memory (look-back: the predecessor always started earlier, possibly in this very warp).
         for (int fb = 0; fb < n_feats; fb += kBatch) {
           const int nfb = min(kBatch, n_feats - fb);
+          const unsigned inv_nfb = 0xffffffffu / (unsigned)nfb + 1u;
           ++epoch;
           for (int t = wid; t < n_chunks * nfb; t += kST / 32) {
-            const int chunk = t / nfb, fi = t % nfb;
+            const int chunk = (int)__umulhi((unsigned)t, inv_nfb), fi = t - chunk * nfb;     // t < 2^11: exact
             const int f = s_feats[fb + fi];
             const uint32_t* lst = cur + (size_t)f * w.nt_stride;
             const int i0 = chunk * 128 + lane * 4;
@@ -460,6 +470,13 @@ __global__ void __launch_bounds__(kST, 1) k_small_cv(SmallWave w) {
         // ---- stable partition of every live feature's list (partition_builder.h), node by node in place; a warp per
         // feature again.  Lefts in front of a segment: noted on entering it, like the sums above.
         uint32_t* nxt = lists + (size_t)pp * F * w.nt_stride;
+        // per row: 0 = stays where it is (finished node, or a node that is not partitioned), 1 = goes right, 2 = goes left;
+        // the sweeps below then touch the node tables only for rows that move
+        for (int r = tid; r < ntrain; r += kST) {
+          const uint16_t sl = s_pos[r];
+          s_left[r] = (sl != kNoSlot && S.sfeat[sl] >= 0) ? (uint8_t)(1 + s_left[r]) : (uint8_t)0;
+        }
+        __syncthreads();
         {   // lefts in front of every partitioned node's segment: the earlier partitioned nodes' left counts
           int ol, dummy;
           const int tl = (tid < m && S.sfeat[tid] >= 0) ? S.totL[tid] : 0;
@@ -481,9 +498,10 @@ __global__ void __launch_bounds__(kST, 1) k_small_cv(SmallWave w) {
         const int n_pfeats = s_i[2];
         for (int fb = 0; fb < n_pfeats; fb += kBatch) {
           const int nfb = min(kBatch, n_pfeats - fb);
+          const unsigned inv_nfb = 0xffffffffu / (unsigned)nfb + 1u;
           ++epoch;
           for (int t = wid; t < n_chunks * nfb; t += kST / 32) {
-            const int chunk = t / nfb, fi = t % nfb;
+            const int chunk = (int)__umulhi((unsigned)t, inv_nfb), fi = t - chunk * nfb;     // t < 2^11: exact
             const int f = s_feats[fb + fi];
             const uint32_t* lst = cur + (size_t)f * w.nt_stride;
             uint32_t* out = nxt + (size_t)f * w.nt_stride;
@@ -496,9 +514,9 @@ __global__ void __launch_bounds__(kST, 1) k_small_cv(SmallWave w) {
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
               const int row = (int)(e[k] & 0xffffu);
-              sl[k] = (i0 + k < ntrain) ? s_pos[row] : kNoSlot;
-              if (sl[k] != kNoSlot && S.sfeat[sl[k]] < 0) sl[k] = kNoSlot;     // node not partitioned: rows stay where they are
-              lk[k] = sl[k] != kNoSlot ? (int)s_left[row] : 0;
+              const int code = (i0 + k < ntrain) ? (int)s_left[row] : 0;
+              sl[k] = code ? s_pos[row] : kNoSlot;
+              lk[k] = code == 2;
               pl[k] = tl;                                                      // exclusive, lane-local
               tl += lk[k];
             }
@@ -552,8 +570,9 @@ __global__ void __launch_bounds__(kST, 1) k_small_cv(SmallWave w) {
           for (int r = tid; r < ntrain; r += kST) {
             const uint16_t sl = s_pos[r];
             if (sl == kNoSlot) continue;
-            const int ns = s_left[r] ? S.baseG[sl] : S.baseH[sl];
-            s_pos[r] = (S.sfeat[sl] >= 0 && ns >= 0) ? (uint16_t)ns : kNoSlot;
+            const int code = s_left[r];
+            const int ns = code == 2 ? S.baseG[sl] : S.baseH[sl];
+            s_pos[r] = (code && ns >= 0) ? (uint16_t)ns : kNoSlot;
           }
           __syncthreads();
           if (part) {
