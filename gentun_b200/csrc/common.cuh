@@ -24,7 +24,10 @@ constexpr int kQuantBitsH = 17;     // hessians are near-constant (1 for squared
 constexpr int kPredRows = 2048;     // rows per predict CTA
 constexpr int kMaskWords = 8;       // feature masks: up to 256 features
 constexpr int kMaxWaveInds = 4096;  // individuals per wave (k_predict keeps their job list in shared memory)
-constexpr int kSmallThreads = 1024;  // the shared-memory-resident regime (small.cu): threads per job (one CTA per SM)
+#ifndef GT_SMALL_THREADS
+#define GT_SMALL_THREADS 1024
+#endif
+constexpr int kSmallThreads = GT_SMALL_THREADS;  // the shared-memory-resident regime (small.cu): threads per job (one CTA per SM)
 constexpr int kSmallMaxTrain = 4095; // train rows per fold it takes: 4095 * 2^19 < 2^31 keeps every prefix sum in int32, 8 list elements per thread
 constexpr int kSmallMaxRows = 8192;  // rows (train + test) it takes: predictions live in shared memory
 
