@@ -319,7 +319,7 @@ __global__ void __launch_bounds__(kST, 1) k_small_cv(SmallWave w) {
           const unsigned inv_nfb = 0xffffffffu / (unsigned)nfb + 1u;
           ++epoch;
           for (int t = wid; t < n_chunks * nfb; t += kST / 32) {
-            const int chunk = (int)__umulhi((unsigned)t, inv_nfb), fi = t - chunk * nfb;     // t < 2^11: exact
+            const int chunk = nfb == 1 ? t : (int)__umulhi((unsigned)t, inv_nfb), fi = t - chunk * nfb;     // t < 2^11: exact (2^32 / 1 does not fit the reciprocal)
             const int f = s_feats[fb + fi];
             const uint32_t* lst = cur + (size_t)f * w.nt_stride;
             const int i0 = chunk * 128 + lane * 4;
@@ -501,7 +501,7 @@ __global__ void __launch_bounds__(kST, 1) k_small_cv(SmallWave w) {
           const unsigned inv_nfb = 0xffffffffu / (unsigned)nfb + 1u;
           ++epoch;
           for (int t = wid; t < n_chunks * nfb; t += kST / 32) {
-            const int chunk = (int)__umulhi((unsigned)t, inv_nfb), fi = t - chunk * nfb;     // t < 2^11: exact
+            const int chunk = nfb == 1 ? t : (int)__umulhi((unsigned)t, inv_nfb), fi = t - chunk * nfb;     // t < 2^11: exact (2^32 / 1 does not fit the reciprocal)
             const int f = s_feats[fb + fi];
             const uint32_t* lst = cur + (size_t)f * w.nt_stride;
             uint32_t* out = nxt + (size_t)f * w.nt_stride;
