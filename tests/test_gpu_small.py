@@ -56,9 +56,9 @@ def test_small_regime_early_stopping_and_seeded_population(wine_engines, wine_np
     ctx.close()
 
 
-@pytest.mark.parametrize("n,f,nfold,cls", [(2500, 7, 5, False), (4000, 40, 4, True), (130, 3, 2, False), (300, 1, 2, False)])
+@pytest.mark.parametrize("n,f,nfold,cls", [(2500, 7, 5, False), (4000, 40, 4, True), (130, 3, 2, False), (300, 1, 2, False), (8190, 5, 2, False)])
 def test_small_regime_other_shapes(n, f, nfold, cls):
-    """Other fold counts, more than 32 features (two mask words), logistic / logloss, a tiny set, a single feature."""
+    """Other fold counts, more than 32 features (two mask words), logistic / logloss, a tiny set, a single feature, the largest train slice the regime takes (4095 rows = 32 chunks)."""
     from gentun_b200.engine import Engine
     x, y = make_dataset(n, f, seed=40 + f, classification=cls)
     small, big = Engine(x, y), Engine(x, y, streaming_only=True)
