@@ -5,6 +5,7 @@
 // 'test-<metric>-mean' last-row read (:37), for a whole batch of gene sets
 // (Population.get_fittest, gentun/populations.py:55-58, evaluates them one by one).
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -44,6 +45,23 @@ int fail(int code, const char* fmt, ...) {
 
 // ---- numpy legacy RandomState stream (np.random.seed(s); np.random.permutation(n)), as used by
 // xgboost training.py mknfold.  MT19937 + masked-rejection interval + Fisher-Yates from the top.
+// GENTUN_B200_TRACE=1: wall-clock milliseconds of the set-up phases on stderr (each mark drains the stream first)
+struct PhaseTrace {
+  bool on; cudaStream_t s; const char* what; std::chrono::steady_clock::time_point t;
+  PhaseTrace(const char* what_, cudaStream_t s_) : on(getenv("GENTUN_B200_TRACE") != nullptr), s(s_), what(what_), t(std::chrono::steady_clock::now()) {}
+  void mark(const char* phase) {
+    if (!on) return;
+    cudaStreamSynchronize(s);
+    const auto now = std::chrono::steady_clock::now();
+    fprintf(stderr, "[gentun_b200] %s: %-28s %9.2f ms\n", what, phase, std::chrono::duration<double, std::milli>(now - t).count());
+    t = now;
+  }
+};
+
+#ifdef GT_SKETCH_PROF
+extern "C" void dump_sketch_prof();
+#endif
+
 struct Mt19937 {
   uint32_t s[624];
   int at;
@@ -78,10 +96,14 @@ struct Mt19937 {
   }
 };
 
-void make_folds_host(int64_t n, int32_t nfold, uint32_t seed, int64_t* perm, int64_t* fold_begin) {
+void make_perm_host(int64_t n, uint32_t seed, int64_t* perm) {   // np.random.seed(seed); np.random.permutation(n)
   Mt19937 rng(seed);
   for (int64_t i = 0; i < n; ++i) perm[i] = i;
   for (int64_t i = n - 1; i > 0; --i) std::swap(perm[i], perm[(int64_t)rng.below_or_equal((uint64_t)i)]);
+}
+
+void make_folds_host(int64_t n, int32_t nfold, uint32_t seed, int64_t* perm, int64_t* fold_begin) {
+  if (perm) make_perm_host(n, seed, perm);
   int64_t q = n / nfold, r = n % nfold, at = 0;   // np.array_split
   for (int k = 0; k < nfold; ++k) { fold_begin[k] = at; at += q + (k < r ? 1 : 0); }
   fold_begin[nfold] = at;
@@ -104,7 +126,7 @@ struct DevBuf {
 
 struct FoldSet {
   int nfold = 0;
-  std::vector<int64_t> perm, fold_begin;
+  std::vector<int64_t> fold_begin;
   std::vector<int64_t> ntrain, ntest;
   std::vector<std::vector<uint32_t>> rows;   // fold order: train slice then test slice
   std::vector<DevBuf<uint32_t>> d_rows;
@@ -154,6 +176,10 @@ struct gt_engine {
   const float* d_y = nullptr;
   DevBuf<float> own_X, own_y;
   std::vector<float> h_y;
+  // xgb.cv's row permutation depends on n alone (seed 0), not on nfold: a helper thread draws it (a serial Mersenne
+  // Twister shuffle, 0.2 s at 10 M rows) while gt_engine_create copies the matrix to the device
+  std::vector<int64_t> perm;
+  std::thread perm_thread;
   int64_t mem_budget = 0;
   int collect_timing = 0;
   std::map<int, std::unique_ptr<FoldSet>> foldsets;
@@ -184,8 +210,13 @@ int prepare_impl(gt_engine* e, int nfold, FoldSet** out) {
   fs->nfold = nfold;
   const int64_t n = e->n;
   const int f = e->f;
-  fs->perm.resize(n); fs->fold_begin.resize(nfold + 1);
-  make_folds_host(n, nfold, 0u, fs->perm.data(), fs->fold_begin.data());
+  fs->fold_begin.resize(nfold + 1);
+  PhaseTrace trace("prepare", e->stream);
+  if (e->perm_thread.joinable()) e->perm_thread.join();
+  if ((int64_t)e->perm.size() != n) { e->perm.resize(n); make_perm_host(n, 0u, e->perm.data()); }
+  make_folds_host(n, nfold, 0u, nullptr, fs->fold_begin.data());
+  const std::vector<int64_t>& perm = e->perm;
+  trace.mark("fold permutation (host)");
   fs->ntrain.resize(nfold); fs->ntest.resize(nfold); fs->rows.resize(nfold);
   fs->d_rows.resize(nfold); fs->d_bins.resize(nfold); fs->d_bins_col.resize(nfold); fs->d_y.resize(nfold); fs->d_count_hist.resize(nfold);
   fs->sum_not1_sq.assign(nfold, 0); fs->sum_not1_lg.assign(nfold, 0); fs->n1.assign(nfold, 0); fs->nnot1.assign(nfold, 0);
@@ -197,19 +228,41 @@ int prepare_impl(gt_engine* e, int nfold, FoldSet** out) {
   std::vector<long long> h_ntrain(nfold);
   std::vector<int> h_limit(nfold);
   size_t lmax = 1, nlevel_max = 1;
+  // every fold's row order (DMatrix.slice(np.concatenate(other chunks)), then the test chunk) and label sums: independent
+  // per fold and bound by the host's memory latency, so one thread each
+  auto fold_rows_and_sums = [&](int k) {
+    auto& rows = fs->rows[k];
+    rows.resize(n);
+    size_t o = 0;
+    for (int c = 0; c < nfold; ++c) {
+      if (c == k) continue;
+      for (int64_t q = fs->fold_begin[c]; q < fs->fold_begin[c + 1]; ++q) rows[o++] = (uint32_t)perm[q];
+    }
+    for (int64_t q = fs->fold_begin[k]; q < fs->fold_begin[k + 1]; ++q) rows[o++] = (uint32_t)perm[q];
+    int64_t n1 = 0, nnot1 = 0;
+    double ssq = 0, slg = 0;
+    for (int64_t q = 0; q < fs->ntrain[k]; ++q) {
+      float y = e->h_y[rows[q]];
+      if (y == 1.0f) n1++;
+      else { nnot1++; ssq += (double)(0.0f - y); slg += (double)(0.5f - y); }
+    }
+    fs->n1[k] = n1; fs->nnot1[k] = nnot1; fs->sum_not1_sq[k] = ssq; fs->sum_not1_lg[k] = slg;
+  };
   for (int k = 0; k < nfold; ++k) {
     int64_t nt = fs->fold_begin[k + 1] - fs->fold_begin[k];
     fs->ntest[k] = nt; fs->ntrain[k] = n - nt;
-    auto& rows = fs->rows[k];
-    rows.resize(n);
-    size_t o = 0;   // DMatrix.slice(np.concatenate(other chunks)) then the test chunk
-    for (int c = 0; c < nfold; ++c) {
-      if (c == k) continue;
-      for (int64_t q = fs->fold_begin[c]; q < fs->fold_begin[c + 1]; ++q) rows[o++] = (uint32_t)fs->perm[q];
-    }
-    for (int64_t q = fs->fold_begin[k]; q < fs->fold_begin[k + 1]; ++q) rows[o++] = (uint32_t)fs->perm[q];
+  }
+  if (n >= (1 << 16)) {
+    std::vector<std::thread> pool;
+    for (int k = 1; k < nfold; ++k) pool.emplace_back(fold_rows_and_sums, k);
+    fold_rows_and_sums(0);
+    for (auto& th : pool) th.join();
+  } else {
+    for (int k = 0; k < nfold; ++k) fold_rows_and_sums(k);
+  }
+  for (int k = 0; k < nfold; ++k) {
     GT_CUDA(fs->d_rows[k].ensure(n));
-    GT_CUDA(cudaMemcpyAsync(fs->d_rows[k].p, rows.data(), sizeof(uint32_t) * n, cudaMemcpyHostToDevice, e->stream));
+    GT_CUDA(cudaMemcpyAsync(fs->d_rows[k].p, fs->rows[k].data(), sizeof(uint32_t) * n, cudaMemcpyHostToDevice, e->stream));
     h_row_ptrs[k] = fs->d_rows[k].p;
     h_ntrain[k] = fs->ntrain[k];
     size_t ntr = (size_t)fs->ntrain[k];
@@ -219,12 +272,8 @@ int prepare_impl(gt_engine* e, int nfold, FoldSet** out) {
     limit_size_level(std::max<size_t>(ntr, 1), eps, &nl, &lim);
     h_limit[k] = (int)lim;
     lmax = std::max(lmax, lim); nlevel_max = std::max(nlevel_max, nl);
-    for (int64_t q = 0; q < fs->ntrain[k]; ++q) {
-      float y = e->h_y[rows[q]];
-      if (y == 1.0f) fs->n1[k]++;
-      else { fs->nnot1[k]++; fs->sum_not1_sq[k] += (double)(0.0f - y); fs->sum_not1_lg[k] += (double)(0.5f - y); }
-    }
   }
+  trace.mark("row orders + label sums");
   // ---- sketch -> cuts
   GT_CUDA(fs->d_cuts.ensure((size_t)nfold * f * GT_MAX_BIN));
   GT_CUDA(fs->d_ncuts.ensure((size_t)nfold * f));
@@ -253,6 +302,7 @@ int prepare_impl(gt_engine* e, int nfold, FoldSet** out) {
     GT_CUDA(cudaMemcpyAsync(d_row_ptrs.p, h_row_ptrs.data(), sizeof(void*) * nfold, cudaMemcpyHostToDevice, e->stream));
     GT_CUDA(cudaMemcpyAsync(d_ntrain.p, h_ntrain.data(), sizeof(long long) * nfold, cudaMemcpyHostToDevice, e->stream));
     GT_CUDA(cudaMemcpyAsync(d_limit.p, h_limit.data(), sizeof(int) * nfold, cudaMemcpyHostToDevice, e->stream));
+    if (int crc = gt::configure_sketch()) return fail(GT_ERR_CUDA, "cudaFuncSetAttribute failed: %s", cudaGetErrorString((cudaError_t)crc));
     for (int s0 = 0; s0 < streams; s0 += per_launch) {
       int cnt = std::min(per_launch, streams - s0);
       gt::launch_sketch(e->d_X, e->ldx, f, nfold, d_row_ptrs.p, d_ntrain.p, plan, d_limit.p, keys.p, ents.p,
@@ -261,6 +311,10 @@ int prepare_impl(gt_engine* e, int nfold, FoldSet** out) {
     }
     GT_CUDA(cudaStreamSynchronize(e->stream));   // arenas are released on scope exit
   }
+  trace.mark("sketch -> cuts");
+#ifdef GT_SKETCH_PROF
+  dump_sketch_prof();
+#endif
   // ---- bins + labels in fold order
   std::vector<gt::FoldDev> h_folds(nfold);
   for (int k = 0; k < nfold; ++k) {
@@ -287,6 +341,7 @@ int prepare_impl(gt_engine* e, int nfold, FoldSet** out) {
   fs->h_ncuts.resize((size_t)nfold * f);
   GT_CUDA(cudaMemcpyAsync(fs->h_ncuts.data(), fs->d_ncuts.p, sizeof(int) * (size_t)nfold * f, cudaMemcpyDeviceToHost, e->stream));
   GT_CUDA(cudaStreamSynchronize(e->stream));
+  trace.mark("binning + count histograms");
   std::vector<int> h_maxnc((size_t)nfold * e->groups, 0);
   for (int k = 0; k < nfold; ++k)
     for (int j = 0; j < f; ++j) {
@@ -328,6 +383,7 @@ int prepare_impl(gt_engine* e, int nfold, FoldSet** out) {
   }
   GT_CUDA(cudaEventRecord(ev1, e->stream));
   GT_CUDA(cudaStreamSynchronize(e->stream));
+  trace.mark("tables (+ small-data lists)");
   float ms = 0;
   GT_CUDA(cudaEventElapsedTime(&ms, ev0, ev1));
   fs->prepare_ms = ms;
@@ -831,8 +887,13 @@ int create_impl(const HostMatrix* hm, const float* X_dev_or_null, int64_t n, int
   GT_CUDA(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
   struct StreamGuard {   // the stream dies with a failed create
     gt_engine* e; bool armed = true;
-    ~StreamGuard() { if (armed && e->stream) { cudaStreamDestroy(e->stream); e->stream = nullptr; } }
+    ~StreamGuard() {
+      if (!armed) return;
+      if (e->perm_thread.joinable()) e->perm_thread.join();
+      if (e->stream) { cudaStreamDestroy(e->stream); e->stream = nullptr; }
+    }
   } guard{e.get()};
+  PhaseTrace trace("create", e->stream);
   e->h_y.resize(n);
   if (!hm) {
     e->d_X = X_dev_or_null; e->d_y = (const float*)y;
@@ -845,9 +906,16 @@ int create_impl(const HostMatrix* hm, const float* X_dev_or_null, int64_t n, int
     GT_CUDA(e->own_X.ensure((size_t)n * ldx));
     GT_CUDA(e->own_y.ensure(n));
     GT_CUDA(cudaMemcpyAsync(e->own_y.p, e->h_y.data(), sizeof(float) * n, cudaMemcpyHostToDevice, e->stream));
+    trace.mark("labels + allocation");
+    if (n >= (1 << 16)) {
+      gt_engine* ep = e.get();
+      ep->perm.resize(n);
+      ep->perm_thread = std::thread([ep, n]() { make_perm_host(n, 0u, ep->perm.data()); });
+    }
     int rc = ingest_matrix(e.get(), *hm);
-    if (rc != GT_OK) return rc;
+    if (rc != GT_OK) { if (e->perm_thread.joinable()) e->perm_thread.join(); return rc; }
     e->d_X = e->own_X.p; e->d_y = e->own_y.p;
+    trace.mark("matrix ingestion");
   }
   {
     DevBuf<unsigned long long> d_bad;
@@ -861,6 +929,7 @@ int create_impl(const HostMatrix* hm, const float* X_dev_or_null, int64_t n, int
       return fail(GT_ERR_ARG, "%llu values of X and %llu labels are NaN or inf: xgb.DMatrix would treat NaN as missing and refuse inf; "
                   "this engine has no missing-value path", h_bad[0], h_bad[1]);
   }
+  trace.mark("non-finite check");
   guard.armed = false;
   *out = e.release();
   return GT_OK;
@@ -919,6 +988,7 @@ void gt_engine_destroy(gt_engine* e) {
 #ifdef GT_SMALL_PROF
   dump_small_prof();
 #endif
+  if (e->perm_thread.joinable()) e->perm_thread.join();
   cudaSetDevice(e->device);
   if (e->stream) { cudaStreamSynchronize(e->stream); }
   e->foldsets.clear();

@@ -20,6 +20,7 @@ void launch_sketch(const float* X, long long ldx, int f, int nfold, const uint32
                    const long long* fold_ntrain, const SketchPlan& plan, const int* fold_limit,
                    unsigned long long* key_arena, float4* entry_arena, float* cuts, int* ncuts, int stream0,
                    int count, cudaStream_t s);
+int configure_sketch();   // cudaFuncSetAttribute for k_sketch_cuts' dynamic shared memory (0 on success); per device, before launch_sketch
 void launch_bin(const float* X, long long ldx, int f, int fpad, const uint32_t* rows, long long n,
                 const float* cuts, const int* ncuts, uint8_t* bins, cudaStream_t s);
 void launch_bins_to_columns(const uint8_t* bins, int f, int fpad, long long n, uint8_t* out, cudaStream_t s);

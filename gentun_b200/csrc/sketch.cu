@@ -7,8 +7,10 @@
 // order-dependent streaming algorithm; it is reproduced stream by stream (one CTA per
 // fold x feature), with the queue fill expressed as a run-length scan and the queue sort as a
 // CTA-wide bitonic network, and the summary merge/prune hierarchy walked by one thread.
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstring>
 
 #include "common.cuh"
 #include "kernels.h"
@@ -18,6 +20,15 @@ namespace gt {
 namespace {
 
 constexpr int kSketchThreads = 1024;
+
+#ifdef GT_SKETCH_PROF   // experiment builds: cycles of every CTA's thread 0 by phase, summed
+__device__ unsigned long long g_sketch_prof[8];
+#define SK_PROF_DECL long long prof_t = clock64()
+#define SK_PROF(i) do { if (threadIdx.x == 0) { const long long now__ = clock64(); atomicAdd(&g_sketch_prof[i], (unsigned long long)(now__ - prof_t)); prof_t = now__; } } while (0)
+#else
+#define SK_PROF_DECL
+#define SK_PROF(i)
+#endif
 
 struct Summary { float4* d; int size; };   // float4 = (rmin, rmax, wmin, value)
 
@@ -117,17 +128,66 @@ __device__ __forceinline__ float unordered_bits(uint32_t o) {
   return __uint_as_float(b);
 }
 
-// CTA-wide bitonic sort of n2 (power of two) 64-bit keys living in global memory (L2 resident).
-__device__ void cta_sort(unsigned long long* keys, int n2) {
-  for (int k = 2; k <= n2; k <<= 1) {
-    for (int j = k >> 1; j > 0; j >>= 1) {
-      for (int t = threadIdx.x; t < (n2 >> 1); t += blockDim.x) {
-        int i = ((t / j) * (j << 1)) + (t % j);
-        int l = i + j;
-        bool up = (i & k) == 0;
-        unsigned long long a = keys[i], b = keys[l];
-        if ((a > b) == up) { keys[i] = b; keys[l] = a; }
+// Dynamic shared memory of k_sketch_cuts: one region, used as a block of sort keys or as a table of search keys.
+constexpr int kSortBlock = 16384;                       // 64-bit keys sorted in shared memory at a time (128 KiB)
+constexpr int kTabCap = 43008;                          // floats of a search table (168 KiB): 2 x limit_size for every n < 2^24
+constexpr int kSketchSmem = kTabCap * 4;
+static_assert(kSortBlock * 8 <= kSketchSmem, "the sort block must fit the dynamic shared memory");
+
+// one compare-exchange pass (partner distance j, direction bit k) over a block of B keys in shared memory whose first
+// key has global index base
+__device__ __forceinline__ void smem_pass(unsigned long long* sk, int B, int base, int j, int k) {
+  for (int t = threadIdx.x; t < (B >> 1); t += blockDim.x) {
+    const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+    const int l = i + j;
+    const bool up = ((base + i) & k) == 0;
+    const unsigned long long a = sk[i], b = sk[l];
+    if ((a > b) == up) { sk[i] = b; sk[l] = a; }
+  }
+  __syncthreads();
+}
+
+// CTA-wide bitonic sort of n2 (power of two) 64-bit keys living in global memory.  Every pass whose partner distance
+// fits a block of kSortBlock keys runs in shared memory (a block is loaded once for all such consecutive passes); only
+// the few passes with a longer distance touch global memory, four pairs per thread in flight.
+__device__ void cta_sort(unsigned long long* keys, int n2, unsigned long long* sk) {
+  const int T = (int)blockDim.x;
+  const int B = min(n2, kSortBlock);
+  for (int base = 0; base < n2; base += B) {          // all stages k <= B, block by block
+    for (int t = threadIdx.x; t < B; t += T) sk[t] = keys[base + t];
+    __syncthreads();
+    for (int k = 2; k <= B; k <<= 1)
+      for (int j = k >> 1; j > 0; j >>= 1) smem_pass(sk, B, base, j, k);
+    for (int t = threadIdx.x; t < B; t += T) keys[base + t] = sk[t];
+    __syncthreads();
+  }
+  for (int k = B << 1; k <= n2; k <<= 1) {
+    for (int j = k >> 1; j >= B; j >>= 1) {           // long distances: in global memory
+      const int half = n2 >> 1;
+      for (int t0 = threadIdx.x; t0 < half; t0 += 4 * T) {
+        unsigned long long a[4], b[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int t = t0 + q * T;
+          if (t < half) { const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1)); a[q] = keys[i]; b[q] = keys[i + j]; }
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int t = t0 + q * T;
+          if (t < half) {
+            const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+            const bool up = (i & k) == 0;
+            if ((a[q] > b[q]) == up) { keys[i] = b[q]; keys[i + j] = a[q]; }
+          }
+        }
       }
+      __syncthreads();
+    }
+    for (int base = 0; base < n2; base += B) {        // distances below B of this stage
+      for (int t = threadIdx.x; t < B; t += T) sk[t] = keys[base + t];
+      __syncthreads();
+      for (int j = B >> 1; j > 0; j >>= 1) smem_pass(sk, B, base, j, k);
+      for (int t = threadIdx.x; t < B; t += T) keys[base + t] = sk[t];
       __syncthreads();
     }
   }
@@ -167,6 +227,7 @@ struct CtaScratch {
   int warp_tot2[32];
   int total, total2;
   int flag;
+  float* tab;        // kTabCap floats of dynamic shared memory: the search keys of the summary being searched
 };
 
 // exclusive scan of one int per thread over the CTA (blockDim.x == 1024); *total gets the CTA sum
@@ -236,13 +297,23 @@ __device__ int p_prune(float4* dst, const float4* src, int m, int maxsize, CtaSc
   const int nq = n - 1;                                  // queries k = 1 .. n-1
   const int per = (nq + (int)blockDim.x - 1) / (int)blockDim.x;
   const int klo = 1 + min(nq, (int)threadIdx.x * per), khi = min(n, klo + per);
+  // the keys the walk compares with, rmin + rmax of every entry, once into shared memory: a query is then a binary
+  // search there instead of ~15 dependent loads from global memory
+  const bool tabbed = m <= kTabCap;
+  float* tab = sc.tab;
+  if (tabbed) {
+    __syncthreads();                                     // the table's previous user is done
+    for (int i = threadIdx.x; i < m; i += blockDim.x) { const float4 e = src[i]; tab[i] = __fadd_rn(e.y, e.x); }
+    __syncthreads();
+  }
   auto choose = [&](int k) -> int {                      // chosen source index, or -1 once the walk has hit the end
     const float dx2 = __fmul_rn(2.0f, __fadd_rn(__fdiv_rn(__fmul_rn((float)k, range), fn), begin));
     int lo = 2, hi = m;                                  // count j in [2, m-1] with rmin[j] + rmax[j] <= dx2
     while (lo < hi) {
       const int mid = (lo + hi) >> 1;
-      const float4 e = src[mid];
-      if (dx2 >= __fadd_rn(e.y, e.x)) lo = mid + 1; else hi = mid;
+      float key;
+      if (tabbed) key = tab[mid]; else { const float4 e = src[mid]; key = __fadd_rn(e.y, e.x); }
+      if (dx2 >= key) lo = mid + 1; else hi = mid;
     }
     const int i = lo - 1;
     if (i >= m - 1) return -1;
@@ -278,9 +349,10 @@ __device__ int p_prune(float4* dst, const float4* src, int m, int maxsize, CtaSc
   return size;
 }
 
-__device__ __forceinline__ int lower_bound_value(const float4* s, int n, float v) {
+// first index whose value is not below v; the values come from the shared-memory table when there is one
+__device__ __forceinline__ int lower_bound_value(const float4* s, const float* tab, int n, float v) {
   int lo = 0, hi = n;
-  while (lo < hi) { const int mid = (lo + hi) >> 1; if (s[mid].w < v) lo = mid + 1; else hi = mid; }
+  while (lo < hi) { const int mid = (lo + hi) >> 1; if ((tab ? tab[mid] : s[mid].w) < v) lo = mid + 1; else hi = mid; }
   return lo;
 }
 
@@ -293,17 +365,27 @@ __device__ int p_combine(float4* dst, const float4* A, int na, const float4* B, 
   const int T = (int)blockDim.x;
   const int pa = (na + T - 1) / T, alo = min(na, (int)threadIdx.x * pa), ahi = min(na, alo + pa);
   const int pb = (nb + T - 1) / T, blo = min(nb, (int)threadIdx.x * pb), bhi = min(nb, blo + pb);
+  // both lists' values once into shared memory: the searches below run there
+  const float* tA = nullptr;
+  const float* tB = nullptr;
+  if (na + nb <= kTabCap) {
+    __syncthreads();                                     // the table's previous user is done
+    for (int i = threadIdx.x; i < na; i += T) sc.tab[i] = A[i].w;
+    for (int i = threadIdx.x; i < nb; i += T) sc.tab[na + i] = B[i].w;
+    __syncthreads();
+    tA = sc.tab; tB = sc.tab + na;
+  }
   int ea = 0, eb = 0;
-  for (int i = alo; i < ahi; ++i) { const float v = A[i].w; const int j = lower_bound_value(B, nb, v); ea += (j < nb && B[j].w == v); }
-  for (int j = blo; j < bhi; ++j) { const float v = B[j].w; const int i = lower_bound_value(A, na, v); eb += (i < na && A[i].w == v); }
+  for (int i = alo; i < ahi; ++i) { const float v = tA ? tA[i] : A[i].w; const int j = lower_bound_value(B, tB, nb, v); ea += (j < nb && (tB ? tB[j] : B[j].w) == v); }
+  for (int j = blo; j < bhi; ++j) { const float v = tB ? tB[j] : B[j].w; const int i = lower_bound_value(A, tA, na, v); eb += (i < na && (tA ? tA[i] : A[i].w) == v); }
   int tot_a, tot_b;
   int Ea = cta_excl_scan(ea, sc.warp_tot, &tot_a);
   int Eb = cta_excl_scan(eb, sc.warp_tot2, &tot_b);
   const float armax = A[na - 1].y, brmax = B[nb - 1].y;
   for (int i = alo; i < ahi; ++i) {
     const float4 a = A[i];
-    const int j = lower_bound_value(B, nb, a.w);
-    const bool eq = j < nb && B[j].w == a.w;
+    const int j = lower_bound_value(B, tB, nb, a.w);
+    const bool eq = j < nb && (tB ? tB[j] : B[j].w) == a.w;
     float4 r;
     if (eq) {
       const float4 b = B[j];
@@ -318,8 +400,8 @@ __device__ int p_combine(float4* dst, const float4* A, int na, const float4* B, 
   }
   for (int j = blo; j < bhi; ++j) {
     const float4 b = B[j];
-    const int i = lower_bound_value(A, na, b.w);
-    const bool eq = i < na && A[i].w == b.w;
+    const int i = lower_bound_value(A, tA, na, b.w);
+    const bool eq = i < na && (tA ? tA[i] : A[i].w) == b.w;
     if (!eq) {
       const float aprev = i > 0 ? __fadd_rn(A[i - 1].x, A[i - 1].z) : 0.f;
       const float anext = i < na ? __fsub_rn(A[i].y, A[i].z) : armax;
@@ -363,6 +445,8 @@ k_sketch_cuts(const float* __restrict__ X, long long ldx, int f, int nfold,
   float4* level_space = ent + 3 * buf_cap;
   float* cuts = cuts_out + (size_t)stream * kBins;
 
+  extern __shared__ __align__(16) unsigned char s_dyn[];   // kSketchSmem bytes: sort block / search table
+  unsigned long long* sk = reinterpret_cast<unsigned long long*>(s_dyn);
   __shared__ float sv[kSketchThreads];
   __shared__ int warp_tot[kSketchThreads / 32];
   __shared__ int level_size[40];
@@ -371,7 +455,7 @@ k_sketch_cuts(const float* __restrict__ X, long long ldx, int f, int nfold,
   const bool parallel_ok = n < (1ll << 24);   // ranks stay exact integers in fp32
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
 
-  if (tid == 0) { levels_in_use = 0; for (int l = 0; l < 40; ++l) level_size[l] = 0; }
+  if (tid == 0) { levels_in_use = 0; for (int l = 0; l < 40; ++l) level_size[l] = 0; sc.tab = reinterpret_cast<float*>(s_dyn); }
   for (int i = tid; i < plan.keys_per_stream; i += blockDim.x) keys[i] = 0ull;
   __syncthreads();
 
@@ -383,6 +467,7 @@ k_sketch_cuts(const float* __restrict__ X, long long ldx, int f, int nfold,
   long long pos = 0;
   long long runs_done = 0, chunk_base = 0;
   float lastv = 0.f;
+  SK_PROF_DECL;
   while (pos < n) {
     // ---- queue fill: QuantileSketchTemplate::Push as a run-length scan over one tile of rows
     long long i = pos + tid;
@@ -416,13 +501,16 @@ k_sketch_cuts(const float* __restrict__ X, long long ldx, int f, int nfold,
     runs_done += flags_consumed;
     __syncthreads();   // sv is rewritten by the next tile
     if (overflow) {
+      SK_PROF(0);
       // ---- queue full and the next value differs: MakeSummary + PushTemp
       const int n2 = next_pow2(qcap);
       for (int t = qcap + tid; t < n2; t += blockDim.x) keys[t] = ~0ull;
       __syncthreads();
-      cta_sort(keys, n2);
+      cta_sort(keys, n2, sk);
+      SK_PROF(1);
       if (parallel_ok) {
         temp.size = p_make_summary(keys, qcap, temp.d, sc);
+        SK_PROF(2);
         for (int l = 1;; ++l) {   // QuantileSketchTemplate::PushTemp, all threads in step
           if (tid == 0 && l + 1 > levels_in_use) levels_in_use = l + 1;
           float4* lvd = level_space + (size_t)l * L;
@@ -432,10 +520,13 @@ k_sketch_cuts(const float* __restrict__ X, long long ldx, int f, int nfold,
             const int sz = p_prune(lvd, temp.d, temp.size, L, sc);
             if (tid == 0) level_size[l] = sz;
             __syncthreads();
+            SK_PROF(3);
             break;
           }
           const int l0sz = p_prune(level_space, temp.d, temp.size, L, sc);
+          SK_PROF(3);
           int csz = p_combine(temp.d, level_space, l0sz, lvd, lsz, sc);
+          SK_PROF(4);
           if (csz < 0) {   // never with integer ranks; keep the reference behaviour anyway
             if (tid == 0) { Summary a0 = { level_space, l0sz }, b0 = { lvd, lsz }; s_combine(temp, a0, b0); sc.total = temp.size; }
             __syncthreads();
@@ -479,14 +570,16 @@ k_sketch_cuts(const float* __restrict__ X, long long ldx, int f, int nfold,
       for (int t = tid; t < n2; t += blockDim.x) keys[t] = 0ull;
       chunk_base += qcap;
       __syncthreads();
+      SK_PROF(5);
     }
   }
+  SK_PROF(0);
   // ---- QuantileSketchTemplate::GetSummary, SketchContainerImpl::AllReduce (one worker), MakeCuts
   const int qtail = (int)(runs_done - chunk_base);
   const int n2 = next_pow2(qtail);
   for (int t = qtail + tid; t < n2; t += blockDim.x) keys[t] = ~0ull;
   __syncthreads();
-  cta_sort(keys, n2);
+  cta_sort(keys, n2, sk);
   if (parallel_ok) {
     out.size = p_make_summary(keys, qtail, out.d, sc);
     const int used = levels_in_use;
@@ -562,6 +655,7 @@ k_sketch_cuts(const float* __restrict__ X, long long ldx, int f, int nfold,
     cuts[nc++] = __fadd_rn(cpt, __fadd_rn(fabsf(cpt), 1e-5f));
     ncuts_out[stream] = nc;
   }
+  SK_PROF(6);
 }
 
 // HistogramCuts::SearchBin: index of the first cut strictly greater than x, clamped to the last cut.
@@ -594,12 +688,33 @@ __global__ void k_bin_u8(const float* __restrict__ X, long long ldx, int f, int 
   }
 }
 
-// feature-major copy of the bin matrix: out[j][r] = bins[r][j]
-__global__ void k_bins_to_columns(const uint8_t* __restrict__ bins, int f, int fpad, long long n, uint8_t* __restrict__ out) {
-  const long long total = n * f;
-  for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
-    const long long j = t / n, r = t % n;
-    out[t] = bins[(size_t)r * fpad + j];
+// feature-major copy of the bin matrix: out[j][r] = bins[r][j].  A CTA moves a tile of 128 rows through shared
+// memory: row-major words in (coalesced), 128 consecutive rows of one feature out per warp store.
+constexpr int kColTileRows = 128;
+__global__ void __launch_bounds__(256) k_bins_to_columns(const uint8_t* __restrict__ bins, int f, int fpad, long long n, uint8_t* __restrict__ out) {
+  extern __shared__ __align__(16) uint8_t s_tile[];      // [128][fpad + 4]: the 4-byte skew spreads a column over the banks
+  const int pitch = fpad + 4, words = fpad >> 2;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const long long tiles = (n + kColTileRows - 1) / kColTileRows;
+  for (long long tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+    const long long r0 = tile * kColTileRows;
+    const int rows = (int)min((long long)kColTileRows, n - r0);
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(bins + (size_t)r0 * fpad);
+    for (int t = threadIdx.x; t < rows * words; t += 256) {
+      const int r = t / words, w = t - r * words;
+      *reinterpret_cast<uint32_t*>(s_tile + r * pitch + 4 * w) = src[t];
+    }
+    __syncthreads();
+    for (int j = wid; j < f; j += 8) {                  // lane l: rows 4l .. 4l + 3 of feature j
+      const int r = 4 * lane;
+      uint32_t v = 0;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) if (r + q < rows) v |= (uint32_t)s_tile[(r + q) * pitch + j] << (8 * q);
+      uint8_t* dst = out + (size_t)j * (size_t)n + (size_t)r0 + r;
+      if (r + 3 < rows && ((n & 3) == 0)) *reinterpret_cast<uint32_t*>(dst) = v;     // r0 is a multiple of 128: aligned when n is a multiple of 4
+      else for (int q = 0; q < 4; ++q) if (r + q < rows) dst[q] = (uint8_t)(v >> (8 * q));
+    }
+    __syncthreads();
   }
 }
 
@@ -613,8 +728,24 @@ void launch_sketch(const float* X, long long ldx, int f, int nfold, const uint32
                    const long long* fold_ntrain, const SketchPlan& plan, const int* fold_limit,
                    unsigned long long* key_arena, float4* entry_arena, float* cuts, int* ncuts, int stream0,
                    int count, cudaStream_t s) {
-  k_sketch_cuts<<<count, kSketchThreads, 0, s>>>(X, ldx, f, nfold, fold_rows, fold_ntrain, plan, fold_limit,
-                                                 key_arena, entry_arena, cuts, ncuts, stream0);
+  k_sketch_cuts<<<count, kSketchThreads, kSketchSmem, s>>>(X, ldx, f, nfold, fold_rows, fold_ntrain, plan, fold_limit,
+                                                           key_arena, entry_arena, cuts, ncuts, stream0);
+}
+
+#ifdef GT_SKETCH_PROF
+extern "C" void dump_sketch_prof() {
+  unsigned long long h[8];
+  cudaMemcpyFromSymbol(h, g_sketch_prof, sizeof(h));
+  const char* names[] = {"queue fill", "sort", "make summary", "prune", "combine", "copy + clear", "final merge + cuts"};
+  unsigned long long tot = 0; for (int i = 0; i < 7; ++i) tot += h[i];
+  for (int i = 0; i < 7; ++i) fprintf(stderr, "sketch prof %-18s %6.2f%%  %llu cycles\n", names[i], 100.0 * h[i] / (double)tot, h[i]);
+  memset(h, 0, sizeof(h));
+  cudaMemcpyToSymbol(g_sketch_prof, h, sizeof(h));
+}
+#endif
+
+int configure_sketch() {   // once per device before the first launch_sketch: the kernel's dynamic shared memory is above 48 KB
+  return (int)cudaFuncSetAttribute(k_sketch_cuts, cudaFuncAttributeMaxDynamicSharedMemorySize, kSketchSmem);
 }
 
 void launch_bin(const float* X, long long ldx, int f, int fpad, const uint32_t* rows, long long n,
@@ -626,7 +757,9 @@ void launch_bin(const float* X, long long ldx, int f, int fpad, const uint32_t* 
 }
 
 void launch_bins_to_columns(const uint8_t* bins, int f, int fpad, long long n, uint8_t* out, cudaStream_t s) {
-  k_bins_to_columns<<<148 * 16, 256, 0, s>>>(bins, f, fpad, n, out);
+  const long long tiles = (n + kColTileRows - 1) / kColTileRows;
+  const int smem = kColTileRows * (fpad + 4);            // 33 KB at 256 features: below the 48 KB that need no opt-in
+  k_bins_to_columns<<<(int)std::min<long long>(tiles, 148 * 8), 256, smem, s>>>(bins, f, fpad, n, out);
 }
 
 // xgb.DMatrix treats NaN as "missing" and refuses inf; this engine has no missing-value path, so both are counted
@@ -689,17 +822,37 @@ void launch_ingest_tile(const void* tile, int dtype, int colmajor, long long ld,
   }
 }
 // train rows per (feature, bin) of one fold, in the cell order of a node histogram ([group][bin][feature lane])
+// rows per (feature, bin) of a fold's train slice, in the histogram layout [group][bin][lane].  A CTA counts one
+// feature group of a run of rows in shared memory (lane = feature: conflict-free banks), then adds its table to the
+// global one.
+constexpr int kCountRowsPerCta = 16384;
 static __global__ void __launch_bounds__(256) k_count_hist(const uint8_t* __restrict__ bins, int f, int fpad, long long ntrain, int* __restrict__ out) {
-  const long long total = ntrain * f;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const long long r = i / f;
-    const int c = (int)(i - r * f);
-    const int b = bins[r * fpad + c];
-    atomicAdd(&out[((c / kLanes) * kBins + b) * kLanes + (c % kLanes)], 1);
+  __shared__ int s_cnt[kBins * kLanes];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int g = blockIdx.y;
+  const bool real = g * kLanes + lane < f;               // the padding lanes of the last group stay zero
+  for (int i = threadIdx.x; i < kBins * kLanes; i += 256) s_cnt[i] = 0;
+  __syncthreads();
+  const long long r0 = (long long)blockIdx.x * kCountRowsPerCta, r1 = min(ntrain, r0 + kCountRowsPerCta);
+  // a warp takes 4 rows per step: lane l loads word (l & 7) of row (l >> 3), then every lane collects the byte of its
+  // own feature from each of the four rows
+  for (long long r = r0 + 4 * wid; r < r1; r += 32) {
+    const long long rr = r + (lane >> 3);
+    const uint32_t word = rr < r1 ? *reinterpret_cast<const uint32_t*>(bins + (size_t)rr * fpad + (size_t)g * kLanes + 4 * (lane & 7)) : 0u;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const uint32_t wq = __shfl_sync(0xffffffffu, word, q * 8 + (lane >> 2));
+      if (real && r + q < r1) atomicAdd(&s_cnt[((wq >> (8 * (lane & 3))) & 255u) * kLanes + lane], 1);
+    }
   }
+  __syncthreads();
+  int* dst = out + (size_t)g * kBins * kLanes;
+  for (int i = threadIdx.x; i < kBins * kLanes; i += 256) { const int c = s_cnt[i]; if (c) atomicAdd(&dst[i], c); }
 }
 void launch_count_hist(const uint8_t* bins, int f, int fpad, long long ntrain, int* out /* zeroed */, cudaStream_t s) {
-  k_count_hist<<<148 * 8, 256, 0, s>>>(bins, f, fpad, ntrain, out);
+  if (ntrain < 1) return;
+  dim3 grid((unsigned)((ntrain + kCountRowsPerCta - 1) / kCountRowsPerCta), (unsigned)(fpad / kLanes));
+  k_count_hist<<<grid, 256, 0, s>>>(bins, f, fpad, ntrain, out);
 }
 void launch_gather_y(const float* y, const uint32_t* rows, long long n, float* out, cudaStream_t s) {
   int blocks = (int)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
@@ -791,6 +944,8 @@ extern "C" int gt_column_cuts_noalloc(const float* d_values, int64_t n, float* d
     void* p = nullptr;
     ce = cudaGetSymbolAddress(&p, g_cut_scratch);
     if (ce != cudaSuccess || !p) return na_fail(GT_ERR_CUDA, "cudaGetSymbolAddress failed: ", cudaGetErrorString(ce));
+    ce = cudaFuncSetAttribute(k_sketch_cuts, cudaFuncAttributeMaxDynamicSharedMemorySize, kSketchSmem);   // no allocation: a launch attribute
+    if (ce != cudaSuccess) return na_fail(GT_ERR_CUDA, "cudaFuncSetAttribute failed: ", cudaGetErrorString(ce));
     g_scratch_on_device[dev] = static_cast<unsigned char*>(p);
   }
   unsigned char* base = g_scratch_on_device[dev];
@@ -809,7 +964,7 @@ extern "C" int gt_column_cuts_noalloc(const float* d_values, int64_t n, float* d
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int blocks = (int)((n + 255) / 256 < 64 ? (n + 255) / 256 : 64);
   k_noalloc_setup<<<blocks, 256, 0, s>>>((long long)n, (int)limit);
-  k_sketch_cuts<<<1, kSketchThreads, 0, s>>>(d_values, 1, 1, 1, reinterpret_cast<const uint32_t* const*>(base),
+  k_sketch_cuts<<<1, kSketchThreads, kSketchSmem, s>>>(d_values, 1, 1, 1, reinterpret_cast<const uint32_t* const*>(base),
                                              reinterpret_cast<const long long*>(base + 8), plan, reinterpret_cast<const int*>(base + 16),
                                              reinterpret_cast<unsigned long long*>(base + kNaKeysOff),
                                              reinterpret_cast<float4*>(base + kNaEntsOff), d_cuts, d_ncuts, 0);
