@@ -128,68 +128,118 @@ __device__ __forceinline__ float unordered_bits(uint32_t o) {
   return __uint_as_float(b);
 }
 
-// Dynamic shared memory of k_sketch_cuts: one region, used as a block of sort keys or as a table of search keys.
-constexpr int kSortBlock = 16384;                       // 64-bit keys sorted in shared memory at a time (128 KiB)
+// Dynamic shared memory of k_sketch_cuts: one region, used by the sort (two padded blocks of keys) or as a table of
+// search keys.
+constexpr int kSortBlock = 8192;                        // keys sorted in shared memory at a time: 8 per thread
+constexpr int kSortPer = kSortBlock / kSketchThreads;
+constexpr int kSortPadded = kSortBlock + kSortBlock / 8;   // one idle slot per 8 keys: neighbouring threads' windows fall on different banks
 constexpr int kTabCap = 43008;                          // floats of a search table (168 KiB): 2 x limit_size for every n < 2^24
 constexpr int kSketchSmem = kTabCap * 4;
-static_assert(kSortBlock * 8 <= kSketchSmem, "the sort block must fit the dynamic shared memory");
+static_assert(2 * kSortPadded * 8 <= kSketchSmem, "the sort's two blocks must fit the dynamic shared memory");
+static_assert(kSortPer == 8, "the register stage sorts 8 keys per thread");
 
-// one compare-exchange pass (partner distance j, direction bit k) over a block of B keys in shared memory whose first
-// key has global index base
-__device__ __forceinline__ void smem_pass(unsigned long long* sk, int B, int base, int j, int k) {
-  for (int t = threadIdx.x; t < (B >> 1); t += blockDim.x) {
-    const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
-    const int l = i + j;
-    const bool up = ((base + i) & k) == 0;
-    const unsigned long long a = sk[i], b = sk[l];
-    if ((a > b) == up) { sk[i] = b; sk[l] = a; }
-  }
-  __syncthreads();
-}
+__device__ __forceinline__ int sort_slot(int i) { return i + (i >> 3); }
 
-// CTA-wide bitonic sort of n2 (power of two) 64-bit keys living in global memory.  Every pass whose partner distance
-// fits a block of kSortBlock keys runs in shared memory (a block is loaded once for all such consecutive passes); only
-// the few passes with a longer distance touch global memory, four pairs per thread in flight.
-__device__ void cta_sort(unsigned long long* keys, int n2, unsigned long long* sk) {
-  const int T = (int)blockDim.x;
-  const int B = min(n2, kSortBlock);
-  for (int base = 0; base < n2; base += B) {          // all stages k <= B, block by block
-    for (int t = threadIdx.x; t < B; t += T) sk[t] = keys[base + t];
-    __syncthreads();
-    for (int k = 2; k <= B; k <<= 1)
-      for (int j = k >> 1; j > 0; j >>= 1) smem_pass(sk, B, base, j, k);
-    for (int t = threadIdx.x; t < B; t += T) keys[base + t] = sk[t];
-    __syncthreads();
-  }
-  for (int k = B << 1; k <= n2; k <<= 1) {
-    for (int j = k >> 1; j >= B; j >>= 1) {           // long distances: in global memory
-      const int half = n2 >> 1;
-      for (int t0 = threadIdx.x; t0 < half; t0 += 4 * T) {
-        unsigned long long a[4], b[4];
+// Merge path: how many of the first `diag` outputs of merge(A, B) come from A (equal keys are identical, so the
+// tie rule is immaterial).  KEY(array, index) reads one key.
+#define GT_MERGE_PATH(A_AT, B_AT, lenA, lenB, diag, result)                              \
+  do {                                                                                    \
+    int lo__ = max(0, (diag) - (lenB)), hi__ = min((diag), (lenA));                       \
+    while (lo__ < hi__) {                                                                 \
+      const int mid__ = (lo__ + hi__) >> 1;                                               \
+      if (A_AT(mid__) <= B_AT((diag) - 1 - mid__)) lo__ = mid__ + 1; else hi__ = mid__;   \
+    }                                                                                     \
+    (result) = lo__;                                                                      \
+  } while (0)
+
+// CTA-wide sort of `count` 64-bit keys in global memory (every key below ~0).  Merge sort: blocks of 8192 keys are
+// sorted in shared memory (8 keys per thread in registers, then ten rounds of pairwise run merges, each thread
+// producing 8 consecutive outputs found by merge path), then the sorted blocks are merged pairwise in global memory,
+// ping-ponging between keys and scratch (count keys of room).  The result ends in keys.
+__device__ void cta_sort(unsigned long long* keys, int count, unsigned long long* scratch, unsigned long long* sm) {
+  const int tid = threadIdx.x;
+  unsigned long long* buf0 = sm;
+  unsigned long long* buf1 = sm + kSortPadded;
+  for (int base = 0; base < count; base += kSortBlock) {
+    const int real = min(kSortBlock, count - base);
+    unsigned long long r[kSortPer];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const int t = t0 + q * T;
-          if (t < half) { const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1)); a[q] = keys[i]; b[q] = keys[i + j]; }
-        }
+    for (int q = 0; q < kSortPer; ++q) {                 // thread t: keys t, t + 1024, ... (coalesced), any order will do
+      const int i = q * kSketchThreads + tid;
+      r[q] = i < real ? keys[base + i] : ~0ull;
+    }
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const int t = t0 + q * T;
-          if (t < half) {
-            const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
-            const bool up = (i & k) == 0;
-            if ((a[q] > b[q]) == up) { keys[i] = b[q]; keys[i + j] = a[q]; }
-          }
-        }
+    for (int round = 0; round < kSortPer; ++round) {     // odd-even transposition sort of the thread's 8 keys
+#pragma unroll
+      for (int q = round & 1; q + 1 < kSortPer; q += 2) {
+        const unsigned long long lo = r[q] < r[q + 1] ? r[q] : r[q + 1], hi = r[q] < r[q + 1] ? r[q + 1] : r[q];
+        r[q] = lo; r[q + 1] = hi;
       }
-      __syncthreads();
     }
-    for (int base = 0; base < n2; base += B) {        // distances below B of this stage
-      for (int t = threadIdx.x; t < B; t += T) sk[t] = keys[base + t];
+#pragma unroll
+    for (int q = 0; q < kSortPer; ++q) buf0[sort_slot(tid * kSortPer + q)] = r[q];
+    __syncthreads();
+    unsigned long long* src = buf0;
+    unsigned long long* dst = buf1;
+    for (int W = kSortPer; W < kSortBlock; W <<= 1) {
+      const int o0 = tid * kSortPer;
+      const int pair0 = o0 & ~(2 * W - 1), diag = o0 - pair0;
+      const unsigned long long* A = src;
+#define A_AT(i) A[sort_slot(pair0 + (i))]
+#define B_AT(i) A[sort_slot(pair0 + W + (i))]
+      int ai;
+      GT_MERGE_PATH(A_AT, B_AT, W, W, diag, ai);
+      int bi = diag - ai;
+      unsigned long long a = ai < W ? A_AT(ai) : ~0ull, b = bi < W ? B_AT(bi) : ~0ull;
+#pragma unroll
+      for (int q = 0; q < kSortPer; ++q) {
+        const bool take_a = bi >= W || (ai < W && a <= b);
+        r[q] = take_a ? a : b;
+        if (take_a) { ++ai; a = ai < W ? A_AT(ai) : ~0ull; } else { ++bi; b = bi < W ? B_AT(bi) : ~0ull; }
+      }
+#undef A_AT
+#undef B_AT
+#pragma unroll
+      for (int q = 0; q < kSortPer; ++q) dst[sort_slot(o0 + q)] = r[q];
       __syncthreads();
-      for (int j = B >> 1; j > 0; j >>= 1) smem_pass(sk, B, base, j, k);
-      for (int t = threadIdx.x; t < B; t += T) keys[base + t] = sk[t];
-      __syncthreads();
+      unsigned long long* t = src; src = dst; dst = t;
     }
+    for (int i = tid; i < real; i += kSketchThreads) keys[base + i] = src[sort_slot(i)];
+    __syncthreads();
+  }
+  // sorted blocks -> one sorted array: pairwise merges of runs of W keys (the last run may be shorter, or alone)
+  unsigned long long* from = keys;
+  unsigned long long* to = scratch;
+  constexpr int S = 32;                                  // outputs per thread and step; divides every run length
+  for (int W = kSortBlock; W < count; W <<= 1) {
+    const int nseg = (count + S - 1) / S;
+    for (int sg = tid; sg < nseg; sg += kSketchThreads) {
+      const int o0 = sg * S;
+      const int pair0 = (o0 / (2 * W)) * (2 * W), diag = o0 - pair0;
+      const int lenA = min(W, count - pair0), lenB = max(0, min(W, count - pair0 - W));
+      const unsigned long long* A = from + pair0;
+      const unsigned long long* B = A + W;
+#define A_AT(i) A[i]
+#define B_AT(i) B[i]
+      int ai;
+      GT_MERGE_PATH(A_AT, B_AT, lenA, lenB, diag, ai);
+#undef A_AT
+#undef B_AT
+      int bi = diag - ai;
+      const int nout = min(S, count - o0);
+      unsigned long long a = ai < lenA ? A[ai] : ~0ull, b = bi < lenB ? B[bi] : ~0ull;
+      for (int q = 0; q < nout; ++q) {
+        const bool take_a = bi >= lenB || (ai < lenA && a <= b);
+        to[o0 + q] = take_a ? a : b;
+        if (take_a) { ++ai; a = ai < lenA ? A[ai] : ~0ull; } else { ++bi; b = bi < lenB ? B[bi] : ~0ull; }
+      }
+    }
+    __syncthreads();
+    unsigned long long* t = from; from = to; to = t;
+  }
+  if (from != keys) {
+    for (int i = tid; i < count; i += kSketchThreads) keys[i] = from[i];
+    __syncthreads();
   }
 }
 
@@ -504,9 +554,7 @@ k_sketch_cuts(const float* __restrict__ X, long long ldx, int f, int nfold,
       SK_PROF(0);
       // ---- queue full and the next value differs: MakeSummary + PushTemp
       const int n2 = next_pow2(qcap);
-      for (int t = qcap + tid; t < n2; t += blockDim.x) keys[t] = ~0ull;
-      __syncthreads();
-      cta_sort(keys, n2, sk);
+      cta_sort(keys, qcap, reinterpret_cast<unsigned long long*>(red.d), sk);
       SK_PROF(1);
       if (parallel_ok) {
         temp.size = p_make_summary(keys, qcap, temp.d, sc);
@@ -576,10 +624,7 @@ k_sketch_cuts(const float* __restrict__ X, long long ldx, int f, int nfold,
   SK_PROF(0);
   // ---- QuantileSketchTemplate::GetSummary, SketchContainerImpl::AllReduce (one worker), MakeCuts
   const int qtail = (int)(runs_done - chunk_base);
-  const int n2 = next_pow2(qtail);
-  for (int t = qtail + tid; t < n2; t += blockDim.x) keys[t] = ~0ull;
-  __syncthreads();
-  cta_sort(keys, n2, sk);
+  cta_sort(keys, qtail, reinterpret_cast<unsigned long long*>(red.d), sk);
   if (parallel_ok) {
     out.size = p_make_summary(keys, qtail, out.d, sc);
     const int used = levels_in_use;
