@@ -306,29 +306,46 @@ __device__ void p_copy(float4* dst, const float4* src, int n) {
   __syncthreads();
 }
 
-// Queue::MakeSummary on sorted keys: one entry per distinct value, ranks from the weight prefix
+// Queue::MakeSummary on sorted keys: one entry per distinct value, ranks from the weight prefix.  Every warp takes a
+// contiguous run of the keys 32 at a time (coalesced); starts of distinct values and weights are prefix-summed inside
+// the warp, the warps' totals across the CTA.
 __device__ int p_make_summary(const unsigned long long* keys, int qtail, float4* out, CtaScratch& sc) {
-  const int per = (qtail + (int)blockDim.x - 1) / (int)blockDim.x;
-  const int lo = min(qtail, (int)threadIdx.x * per), hi = min(qtail, lo + per);
-  int starts = 0, wsum = 0;
-  for (int i = lo; i < hi; ++i) {
-    const unsigned long long k = keys[i];
-    const float v = unordered_bits((uint32_t)(k >> 32));
-    const bool st = i == 0 || !(unordered_bits((uint32_t)(keys[i - 1] >> 32)) == v);
-    starts += st;
-    wsum += (int)(uint32_t)k;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (int)blockDim.x >> 5;
+  const int chunk = ((qtail + nw - 1) / nw + 31) / 32 * 32;
+  const int lo = min(qtail, wid * chunk), hi = min(qtail, lo + chunk);
+  int starts = 0, wsum = 0;                              // warp-uniform
+  for (int i0 = lo; i0 < hi; i0 += 32) {
+    const int i = i0 + lane;
+    const bool in = i < hi;
+    const unsigned long long k = in ? keys[i] : 0ull;
+    const unsigned long long kp = in && i > 0 ? keys[i - 1] : 0ull;
+    const bool st = in && (i == 0 || !(unordered_bits((uint32_t)(kp >> 32)) == unordered_bits((uint32_t)(k >> 32))));
+    starts += __popc(__ballot_sync(0xffffffffu, st));
+    wsum += __reduce_add_sync(0xffffffffu, in ? (int)(uint32_t)k : 0);
   }
   int tot_g, tot_w;
-  int g = cta_excl_scan(starts, sc.warp_tot, &tot_g);
-  int w = cta_excl_scan(wsum, sc.warp_tot2, &tot_w);
-  for (int i = lo; i < hi; ++i) {
-    const unsigned long long k = keys[i];
+  int g = cta_excl_scan(lane == 0 ? starts : 0, sc.warp_tot, &tot_g);
+  int w = cta_excl_scan(lane == 0 ? wsum : 0, sc.warp_tot2, &tot_w);
+  g = __shfl_sync(0xffffffffu, g, 0); w = __shfl_sync(0xffffffffu, w, 0);
+  for (int i0 = lo; i0 < hi; i0 += 32) {
+    const int i = i0 + lane;
+    const bool in = i < hi;
+    const unsigned long long k = in ? keys[i] : 0ull;
+    const unsigned long long kp = in && i > 0 ? keys[i - 1] : 0ull;
+    const unsigned long long kn = in && i + 1 < qtail ? keys[i + 1] : 0ull;
     const float v = unordered_bits((uint32_t)(k >> 32));
-    const bool st = i == 0 || !(unordered_bits((uint32_t)(keys[i - 1] >> 32)) == v);
-    if (st) { out[g].x = (float)w; out[g].w = v; ++g; }
-    w += (int)(uint32_t)k;
-    const bool en = i == qtail - 1 || !(unordered_bits((uint32_t)(keys[i + 1] >> 32)) == v);
-    if (en) out[g - 1].y = (float)w;
+    const bool st = in && (i == 0 || !(unordered_bits((uint32_t)(kp >> 32)) == v));
+    const bool en = in && (i == qtail - 1 || !(unordered_bits((uint32_t)(kn >> 32)) == v));
+    const int wt = in ? (int)(uint32_t)k : 0;
+    int incw = wt;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incw, d); if (lane >= d) incw += t; }
+    const unsigned bal = __ballot_sync(0xffffffffu, st);
+    const int idx = g + __popc(bal & (0xffffffffu >> (31 - lane))) - 1;    // the distinct value this key belongs to
+    if (st) { out[idx].x = (float)(w + incw - wt); out[idx].w = v; }
+    if (en) out[idx].y = (float)(w + incw);
+    g += __popc(bal);
+    w += __shfl_sync(0xffffffffu, incw, 31);
   }
   __syncthreads();
   for (int i = threadIdx.x; i < tot_g; i += blockDim.x) { float4 e = out[i]; e.z = __fsub_rn(e.y, e.x); out[i] = e; }
@@ -370,20 +387,23 @@ __device__ int p_prune(float4* dst, const float4* src, int m, int maxsize, CtaSc
     const float4 a = src[i], b = src[i + 1];
     return dx2 < __fadd_rn(__fadd_rn(a.x, a.z), __fsub_rn(b.y, b.z)) ? i : i + 1;
   };
-  int prev = klo > 1 && klo < n ? choose(klo - 1) : 0;   // lastidx seen by this thread's first query
-  int emits = 0;
+  const int prev0 = klo > 1 && klo < n ? choose(klo - 1) : 0;   // lastidx seen by this thread's first query
+  constexpr int kKeep = 24;                              // chosen indices kept from the counting pass (20 queries per thread at most for n < 2^24)
+  int kept[kKeep];
+  int prev = prev0, emits = 0;
   for (int k = klo; k < khi; ++k) {
     const int c = choose(k);
+    if (k - klo < kKeep) kept[k - klo] = c;
     if (c < 0) break;
     emits += (c != prev);
     prev = c;
   }
   int total;
   int pos = 1 + cta_excl_scan(emits, sc.warp_tot, &total);
-  prev = klo > 1 && klo < n ? choose(klo - 1) : 0;
+  prev = prev0;
   int last_c = -2;                                       // chosen index of the last valid query in this range
   for (int k = klo; k < khi; ++k) {
-    const int c = choose(k);
+    const int c = k - klo < kKeep ? kept[k - klo] : choose(k);
     if (c < 0) break;
     if (c != prev) dst[pos++] = src[c];
     prev = c;
@@ -425,16 +445,28 @@ __device__ int p_combine(float4* dst, const float4* A, int na, const float4* B, 
     __syncthreads();
     tA = sc.tab; tB = sc.tab + na;
   }
+  constexpr int kKeep = 24;                              // search results kept from the counting pass (20 elements per thread and list at most for n < 2^24)
+  int ja[kKeep], ib[kKeep];
   int ea = 0, eb = 0;
-  for (int i = alo; i < ahi; ++i) { const float v = tA ? tA[i] : A[i].w; const int j = lower_bound_value(B, tB, nb, v); ea += (j < nb && (tB ? tB[j] : B[j].w) == v); }
-  for (int j = blo; j < bhi; ++j) { const float v = tB ? tB[j] : B[j].w; const int i = lower_bound_value(A, tA, na, v); eb += (i < na && (tA ? tA[i] : A[i].w) == v); }
+  for (int i = alo; i < ahi; ++i) {
+    const float v = tA ? tA[i] : A[i].w;
+    const int j = lower_bound_value(B, tB, nb, v);
+    if (i - alo < kKeep) ja[i - alo] = j;
+    ea += (j < nb && (tB ? tB[j] : B[j].w) == v);
+  }
+  for (int j = blo; j < bhi; ++j) {
+    const float v = tB ? tB[j] : B[j].w;
+    const int i = lower_bound_value(A, tA, na, v);
+    if (j - blo < kKeep) ib[j - blo] = i;
+    eb += (i < na && (tA ? tA[i] : A[i].w) == v);
+  }
   int tot_a, tot_b;
   int Ea = cta_excl_scan(ea, sc.warp_tot, &tot_a);
   int Eb = cta_excl_scan(eb, sc.warp_tot2, &tot_b);
   const float armax = A[na - 1].y, brmax = B[nb - 1].y;
   for (int i = alo; i < ahi; ++i) {
     const float4 a = A[i];
-    const int j = lower_bound_value(B, tB, nb, a.w);
+    const int j = i - alo < kKeep ? ja[i - alo] : lower_bound_value(B, tB, nb, a.w);
     const bool eq = j < nb && (tB ? tB[j] : B[j].w) == a.w;
     float4 r;
     if (eq) {
@@ -450,7 +482,7 @@ __device__ int p_combine(float4* dst, const float4* A, int na, const float4* B, 
   }
   for (int j = blo; j < bhi; ++j) {
     const float4 b = B[j];
-    const int i = lower_bound_value(A, tA, na, b.w);
+    const int i = j - blo < kKeep ? ib[j - blo] : lower_bound_value(A, tA, na, b.w);
     const bool eq = i < na && (tA ? tA[i] : A[i].w) == b.w;
     if (!eq) {
       const float aprev = i > 0 ? __fadd_rn(A[i - 1].x, A[i - 1].z) : 0.f;
