@@ -74,6 +74,24 @@ def test_folds_bit_exact_wine(wine_pair):
     assert np.array_equal(eng.fold_rows(3, 0)[1], perm[:1633])
 
 
+def test_one_engine_several_fold_counts():
+    """The row permutation depends on n alone (np.random.seed(0); permutation(n)) and is drawn once per engine, on a
+    helper thread while the matrix is copied (n >= 65536): every nfold prepared afterwards must cut the same permutation."""
+    from gentun_b200.engine import Engine
+    n = 70001
+    x, y = make_dataset(n, 3, seed=77)
+    eng = Engine(x, y)
+    np.random.seed(0)
+    perm = np.random.permutation(n)
+    for nfold in (3, 2, 7):
+        chunks = np.array_split(perm, nfold)
+        for k in range(nfold):
+            tr, te = eng.fold_rows(nfold, k)
+            assert np.array_equal(te, chunks[k])
+            assert np.array_equal(tr, np.concatenate([c for q, c in enumerate(chunks) if q != k]))
+    eng.close()
+
+
 def test_cuts_and_bins_bit_exact_wine(wine_pair):
     eng, ctx = wine_pair
     for k in range(3):
