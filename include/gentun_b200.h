@@ -105,7 +105,10 @@ int gt_engine_create(const float* X, int64_t n, int32_t f, int64_t ldx, const fl
  * type and layout, no host-side copy or cast by the caller.  Strides are in elements; either x_col_stride == 1
  * (row-major, x_row_stride >= f) or x_row_stride == 1 (column-major, x_col_stride >= n).  The matrix is staged
  * tile by tile through pinned buffers the library keeps, cast to float on the device (the cast DMatrix applies)
- * and laid out row-major there.  y is cast on the host.  opts->x_on_device must be 0. */
+ * and laid out row-major there.  y is cast on the host.  opts->x_on_device must be 0.  While the matrix moves, a
+ * helper thread of the engine draws xgb.cv's row permutation (it depends on n alone); gt_engine_prepare and
+ * gt_engine_destroy join it.  With GENTUN_B200_TRACE set in the environment, create and prepare print the
+ * wall-clock time of their phases on stderr. */
 #define GT_DTYPE_F32 0
 #define GT_DTYPE_F64 1
 #define GT_DTYPE_I64 2   /* labels only */
