@@ -278,7 +278,9 @@ struct CtaScratch {
   int total, total2;
   int flag;
   float* tab;        // kTabCap floats of dynamic shared memory: the search keys of the summary being searched
+  int cnt[2][24 * 32];   // per (row of 1024 elements, warp) counts of the interleaved passes, then their exclusive prefixes
 };
+constexpr int kRowsMax = 24;   // rows of 1024 elements the interleaved passes handle (20 for every n < 2^24); longer lists take the blocked versions
 
 // exclusive scan of one int per thread over the CTA (blockDim.x == 1024); *total gets the CTA sum
 __device__ __forceinline__ int cta_excl_scan(int v, int* warp_tot, int* total) {
@@ -355,7 +357,7 @@ __device__ int p_make_summary(const unsigned long long* keys, int qtail, float4*
 
 // WQSummary::SetPrune.  For query k the sequential walk stops at the first i with dx2 < rmin[i+1] + rmax[i+1];
 // both dx2 (in k) and that sum (in i) are non-decreasing, so i(k) is an upper-bound search.
-__device__ int p_prune(float4* dst, const float4* src, int m, int maxsize, CtaScratch& sc) {
+__device__ int p_prune_blocked(float4* dst, const float4* src, int m, int maxsize, CtaScratch& sc) {
   if (m <= maxsize) { p_copy(dst, src, m); return m; }
   const float begin = src[0].y;
   const float range = __fsub_rn(src[m - 1].x, src[0].y);
@@ -429,7 +431,7 @@ __device__ __forceinline__ int lower_bound_value(const float4* s, const float* t
 // WQSummary::SetCombine: a merge by value in which equal values fuse; every output entry depends only on its
 // own element and on its neighbours in the other list.  Returns the size, or -1 if FixError would have had to
 // change something (impossible with integer ranks; the caller then redoes the combine with one thread).
-__device__ int p_combine(float4* dst, const float4* A, int na, const float4* B, int nb, CtaScratch& sc) {
+__device__ int p_combine_blocked(float4* dst, const float4* A, int na, const float4* B, int nb, CtaScratch& sc) {
   if (na == 0) { p_copy(dst, B, nb); return nb; }
   if (nb == 0) { p_copy(dst, A, na); return na; }
   const int T = (int)blockDim.x;
@@ -496,6 +498,169 @@ __device__ int p_combine(float4* dst, const float4* A, int na, const float4* B, 
   const int size = na + nb - tot_a;
   int bad = 0;                                                                            // FixError would act iff one of these holds
   for (int i = threadIdx.x; i < size; i += T) {
+    const float4 e = dst[i];
+    if (e.y < __fadd_rn(e.x, e.z)) bad = 1;
+    if (i > 0) { const float4 p = dst[i - 1]; if (e.x < p.x || e.y < p.y) bad = 1; }
+  }
+  if (bad) sc.flag = 1;
+  __syncthreads();
+  const int res = sc.flag ? -1 : size;
+  __syncthreads();
+  return res;
+}
+
+// exclusive prefix over the per-(row, warp) counts in sc.cnt[which][0 .. rows * 32), in place; returns the total
+__device__ __forceinline__ int scan_row_counts(CtaScratch& sc, int which, int rows, int* warp_tot) {
+  __syncthreads();
+  const int t = threadIdx.x;
+  const int v = t < rows * 32 ? sc.cnt[which][t] : 0;
+  int total;
+  const int ex = cta_excl_scan(v, warp_tot, &total);
+  if (t < rows * 32) sc.cnt[which][t] = ex;
+  __syncthreads();
+  return total;
+}
+
+// SetPrune with the queries dealt to the threads round-robin (query k = 1 + row * 1024 + thread): the entries that
+// neighbouring lanes read and the outputs they write are neighbours in memory.  Same result as p_prune_blocked.
+__device__ int p_prune(float4* dst, const float4* src, int m, int maxsize, CtaScratch& sc) {
+  if (m <= maxsize) { p_copy(dst, src, m); return m; }
+  const int T = (int)blockDim.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int n = maxsize - 1, nq = n - 1;
+  const int rows = (nq + T - 1) / T;
+  if (rows > kRowsMax || m > kTabCap || T != 1024) return p_prune_blocked(dst, src, m, maxsize, sc);
+  const float begin = src[0].y;
+  const float range = __fsub_rn(src[m - 1].x, src[0].y);
+  const float fn = (float)n;
+  float* tab = sc.tab;
+  __syncthreads();                                       // the table's previous user is done
+  for (int i = tid; i < m; i += T) { const float4 e = src[i]; tab[i] = __fadd_rn(e.y, e.x); }
+  __syncthreads();
+  auto choose = [&](int k) -> int {                      // chosen source index, or -1 once the walk has hit the end
+    const float dx2 = __fmul_rn(2.0f, __fadd_rn(__fdiv_rn(__fmul_rn((float)k, range), fn), begin));
+    int lo = 2, hi = m;                                  // count j in [2, m-1] with rmin[j] + rmax[j] <= dx2
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (dx2 >= tab[mid]) lo = mid + 1; else hi = mid;
+    }
+    const int i = lo - 1;
+    if (i >= m - 1) return -1;
+    const float4 a = src[i], b = src[i + 1];
+    return dx2 < __fadd_rn(__fadd_rn(a.x, a.z), __fsub_rn(b.y, b.z)) ? i : i + 1;
+  };
+  // query k is emitted iff its choice differs from query k-1's (lastidx starts at 0); choices never decrease and
+  // stay -1 once the walk has ended
+  int kept[kRowsMax];
+  unsigned emask = 0u;
+  int last_c = -2;
+#pragma unroll 1
+  for (int q = 0; q < rows; ++q) {
+    const int k = 1 + q * T + tid;
+    const int c = k < n ? choose(k) : -1;
+    kept[q] = c;
+    int pc = __shfl_up_sync(0xffffffffu, c, 1);
+    if (lane == 0) pc = k == 1 ? 0 : (k - 1 < n ? choose(k - 1) : -1);
+    const bool emit = c >= 0 && c != pc;
+    const unsigned bal = __ballot_sync(0xffffffffu, emit);
+    if (lane == 0) sc.cnt[0][q * 32 + wid] = __popc(bal);
+    emask |= (emit ? 1u : 0u) << q;
+    if (c >= 0) last_c = c;
+  }
+  const int total = scan_row_counts(sc, 0, rows, sc.warp_tot);
+#pragma unroll 1
+  for (int q = 0; q < rows; ++q) {
+    const bool emit = (emask >> q) & 1u;
+    const unsigned bal = __ballot_sync(0xffffffffu, emit);
+    if (emit) dst[1 + sc.cnt[0][q * 32 + wid] + __popc(bal & ((1u << lane) - 1u))] = src[kept[q]];
+  }
+  if (tid == 0) { dst[0] = src[0]; sc.flag = 0; }
+  __syncthreads();
+  if (last_c >= 0) atomicMax(&sc.flag, last_c);          // chosen indices never decrease: the max is the final lastidx
+  __syncthreads();
+  int size = 1 + total;
+  if (sc.flag != m - 1) { if (tid == 0) dst[size] = src[m - 1]; ++size; }
+  __syncthreads();
+  return size;
+}
+
+// SetCombine with the elements dealt to the threads round-robin (element = row * 1024 + thread), see p_prune.
+__device__ int p_combine(float4* dst, const float4* A, int na, const float4* B, int nb, CtaScratch& sc) {
+  if (na == 0) { p_copy(dst, B, nb); return nb; }
+  if (nb == 0) { p_copy(dst, A, na); return na; }
+  const int T = (int)blockDim.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int rows_a = (na + T - 1) / T, rows_b = (nb + T - 1) / T;
+  if (rows_a > kRowsMax || rows_b > kRowsMax || na + nb > kTabCap || T != 1024) return p_combine_blocked(dst, A, na, B, nb, sc);
+  __syncthreads();                                       // the table's previous user is done
+  for (int i = tid; i < na; i += T) sc.tab[i] = A[i].w;
+  for (int i = tid; i < nb; i += T) sc.tab[na + i] = B[i].w;
+  __syncthreads();
+  const float* tA = sc.tab;
+  const float* tB = sc.tab + na;
+  int ja[kRowsMax], ib[kRowsMax];
+  unsigned eqa = 0u, eqb = 0u;
+#pragma unroll 1
+  for (int q = 0; q < rows_a; ++q) {
+    const int i = q * T + tid;
+    int j = 0; bool eq = false;
+    if (i < na) { const float v = tA[i]; j = lower_bound_value(B, tB, nb, v); eq = j < nb && tB[j] == v; }
+    ja[q] = j;
+    const unsigned bal = __ballot_sync(0xffffffffu, eq);
+    if (lane == 0) sc.cnt[0][q * 32 + wid] = __popc(bal);
+    eqa |= (eq ? 1u : 0u) << q;
+  }
+#pragma unroll 1
+  for (int q = 0; q < rows_b; ++q) {
+    const int j = q * T + tid;
+    int i = 0; bool eq = false;
+    if (j < nb) { const float v = tB[j]; i = lower_bound_value(A, tA, na, v); eq = i < na && tA[i] == v; }
+    ib[q] = i;
+    const unsigned bal = __ballot_sync(0xffffffffu, eq);
+    if (lane == 0) sc.cnt[1][q * 32 + wid] = __popc(bal);
+    eqb |= (eq ? 1u : 0u) << q;
+  }
+  const int tot_a = scan_row_counts(sc, 0, rows_a, sc.warp_tot);
+  scan_row_counts(sc, 1, rows_b, sc.warp_tot2);
+  const float armax = A[na - 1].y, brmax = B[nb - 1].y;
+#pragma unroll 1
+  for (int q = 0; q < rows_a; ++q) {
+    const int i = q * T + tid;
+    const bool eq = (eqa >> q) & 1u;
+    const unsigned bal = __ballot_sync(0xffffffffu, eq);
+    if (i < na) {
+      const int Ea = sc.cnt[0][q * 32 + wid] + __popc(bal & ((1u << lane) - 1u));   // equal pairs among A's earlier elements
+      const float4 a = A[i];
+      const int j = ja[q];
+      float4 r;
+      if (eq) {
+        const float4 b = B[j];
+        r = make_float4(__fadd_rn(a.x, b.x), __fadd_rn(a.y, b.y), __fadd_rn(a.z, b.z), a.w);
+      } else {
+        const float bprev = j > 0 ? __fadd_rn(B[j - 1].x, B[j - 1].z) : 0.f;               // RMinNext of the last smaller b
+        const float bnext = j < nb ? __fsub_rn(B[j].y, B[j].z) : brmax;                     // RMaxPrev of the next b, or b's last rmax
+        r = make_float4(__fadd_rn(a.x, bprev), __fadd_rn(a.y, bnext), a.z, a.w);
+      }
+      dst[i + j - Ea] = r;
+    }
+  }
+#pragma unroll 1
+  for (int q = 0; q < rows_b; ++q) {
+    const int j = q * T + tid;
+    const bool eq = (eqb >> q) & 1u;
+    const unsigned bal = __ballot_sync(0xffffffffu, eq);
+    if (j < nb && !eq) {
+      const int Eb = sc.cnt[1][q * 32 + wid] + __popc(bal & ((1u << lane) - 1u));
+      const float4 b = B[j];
+      const int i = ib[q];
+      const float aprev = i > 0 ? __fadd_rn(A[i - 1].x, A[i - 1].z) : 0.f;
+      const float anext = i < na ? __fsub_rn(A[i].y, A[i].z) : armax;
+      dst[j + i - Eb] = make_float4(__fadd_rn(b.x, aprev), __fadd_rn(b.y, anext), b.z, b.w);
+    }
+  }
+  if (tid == 0) sc.flag = 0;
+  __syncthreads();
+  const int size = na + nb - tot_a;
+  int bad = 0;                                                                            // FixError would act iff one of these holds
+  for (int i = tid; i < size; i += T) {
     const float4 e = dst[i];
     if (e.y < __fadd_rn(e.x, e.z)) bad = 1;
     if (i > 0) { const float4 p = dst[i - 1]; if (e.x < p.x || e.y < p.y) bad = 1; }
