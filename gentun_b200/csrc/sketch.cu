@@ -672,8 +672,6 @@ __device__ int p_combine(float4* dst, const float4* A, int na, const float4* B, 
   return res;
 }
 
-__device__ __forceinline__ int next_pow2(int v) { int p = 2; while (p < v) p <<= 1; return p; }
-
 __global__ void __launch_bounds__(kSketchThreads)
 k_sketch_cuts(const float* __restrict__ X, long long ldx, int f, int nfold,
               const uint32_t* const* __restrict__ fold_rows, const long long* __restrict__ fold_ntrain,
@@ -750,7 +748,6 @@ k_sketch_cuts(const float* __restrict__ X, long long ldx, int f, int nfold,
     if (overflow) {
       SK_PROF(0);
       // ---- queue full and the next value differs: MakeSummary + PushTemp
-      const int n2 = next_pow2(qcap);
       cta_sort(keys, qcap, reinterpret_cast<unsigned long long*>(red.d), sk);
       SK_PROF(1);
       if (parallel_ok) {
@@ -812,7 +809,7 @@ k_sketch_cuts(const float* __restrict__ X, long long ldx, int f, int nfold,
         }
       }
       __syncthreads();
-      for (int t = tid; t < n2; t += blockDim.x) keys[t] = 0ull;
+      for (int t = tid; t < qcap; t += blockDim.x) keys[t] = 0ull;     // the queue's slots, ready for the next fill
       chunk_base += qcap;
       __syncthreads();
       SK_PROF(5);
