@@ -11,6 +11,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <exception>
 #include <map>
 #include <memory>
 #include <mutex>
@@ -254,8 +255,12 @@ int prepare_impl(gt_engine* e, int nfold, FoldSet** out) {
   }
   if (n >= (1 << 16)) {
     std::vector<std::thread> pool;
-    for (int k = 1; k < nfold; ++k) pool.emplace_back(fold_rows_and_sums, k);
+    int started = 1;                                     // folds [1, started) have a thread; the rest run here
+    try {
+      for (int k = 1; k < nfold; ++k) { pool.emplace_back(fold_rows_and_sums, k); started = k + 1; }
+    } catch (const std::exception&) {}
     fold_rows_and_sums(0);
+    for (int k = started; k < nfold; ++k) fold_rows_and_sums(k);
     for (auto& th : pool) th.join();
   } else {
     for (int k = 0; k < nfold; ++k) fold_rows_and_sums(k);
@@ -850,8 +855,12 @@ int ingest_matrix(gt_engine* e, const HostMatrix& m) {
       const int n_thr = (int)std::max(1u, std::min(std::min(8u, hw ? hw / 2 : 1u), (unsigned)(bytes >> 20)));   // tiles below a few MB: one thread
       auto work = [&](int t) { for (size_t q = (size_t)t; q < piece_ptr.size(); q += (size_t)n_thr) memcpy(piece_ptr[q].second, piece_ptr[q].first, piece_len[q]); };
       std::vector<std::thread> pool;
-      for (int t = 1; t < n_thr; ++t) pool.emplace_back(work, t);
+      int started = 1;                                   // shares [1, started) have a thread; the rest are copied here
+      try {
+        for (int t = 1; t < n_thr; ++t) { pool.emplace_back(work, t); started = t + 1; }
+      } catch (const std::exception&) {}
       work(0);
+      for (int t = started; t < n_thr; ++t) work(t);
       for (auto& th : pool) th.join();
     }
     cudaError_t ce = cudaMemcpyAsync(d_tile[b].p, pin, bytes, cudaMemcpyHostToDevice, e->stream);
@@ -910,7 +919,11 @@ int create_impl(const HostMatrix* hm, const float* X_dev_or_null, int64_t n, int
     if (n >= (1 << 16)) {
       gt_engine* ep = e.get();
       ep->perm.resize(n);
-      ep->perm_thread = std::thread([ep, n]() { make_perm_host(n, 0u, ep->perm.data()); });
+      try {
+        ep->perm_thread = std::thread([ep, n]() { make_perm_host(n, 0u, ep->perm.data()); });
+      } catch (const std::exception&) {   // no thread to be had: gt_engine_prepare draws the permutation itself
+        ep->perm.clear();
+      }
     }
     int rc = ingest_matrix(e.get(), *hm);
     if (rc != GT_OK) { if (e->perm_thread.joinable()) e->perm_thread.join(); return rc; }
