@@ -5,8 +5,9 @@
 // (upstream src/common/quantile.{h,cc}) over the rows of each fold's train slice in slice order,
 // then GHistIndexMatrix binning (upstream src/common/hist_util.h SearchBin).  The sketch is an
 // order-dependent streaming algorithm; it is reproduced stream by stream (one CTA per
-// fold x feature), with the queue fill expressed as a run-length scan and the queue sort as a
-// CTA-wide bitonic network, and the summary merge/prune hierarchy walked by one thread.
+// fold x feature), with the queue fill expressed as a run-length scan, the queue sort as a
+// CTA-wide merge sort in shared memory, and the summary merge/prune hierarchy as CTA-parallel
+// passes (one thread walks it for streams of 2^24 rows or more, where fp32 ranks stop being exact).
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
