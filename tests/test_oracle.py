@@ -73,6 +73,39 @@ def test_cuts_of_small_columns_are_the_distinct_values(wine_ctx, wine):
                 assert nc[j] <= 256 and set(c[:-1]).issubset(set(vals))
 
 
+def test_sketch_cuts_keep_the_quantile_guarantee():
+    """A column with far more rows than the sketch queue (several flushes, prune / combine through the summary levels):
+    WQuantileSketch promises ranks within eps * n of the requested quantiles with eps = 1 / (8 * max_bin), so the cut
+    points must be data values and no bin may hold much more than n / 256 rows -- a property the restatement cannot meet
+    by accident if its prune or combine were wrong.  Continuous, heavily tied and skewed columns."""
+    rng = np.random.default_rng(11)
+    n = 300_000
+    x = np.empty((n, 3), dtype=np.float32)
+    x[:, 0] = rng.standard_normal(n)
+    x[:, 1] = np.round(rng.standard_normal(n) * 40.0)            # ~300 distinct values, heavy ties
+    x[:, 2] = rng.lognormal(0.0, 2.0, n)                         # long right tail
+    y = x[:, 0].copy()
+    ctx = orc.Context(x, y, 2)
+    try:
+        for k in range(2):
+            cu, nc = ctx.cuts(k)
+            rows = ctx.train_rows(k)
+            for j in range(3):
+                col = x[rows, j]
+                c = cu[j, :nc[j]]
+                assert 2 <= nc[j] <= 256 and np.all(np.diff(c) > 0)
+                assert set(c[:-1]).issubset(set(np.unique(col))) and c[-1] > col.max()
+                counts = np.bincount(np.minimum(np.searchsorted(c, col, side="right"), nc[j] - 1), minlength=nc[j])
+                if j == 1:
+                    # ties: a bin cannot be split below one distinct value
+                    biggest_tie = np.unique(col, return_counts=True)[1].max()
+                    assert counts.max() <= biggest_tie + 2 * len(col) / 256
+                else:
+                    assert counts.max() <= 2.0 * len(col) / 256, (j, counts.max(), len(col) / 256)
+    finally:
+        ctx.close()
+
+
 def test_bins_are_upper_bound_of_cuts(wine_ctx, wine):
     x = wine[0].values.astype(np.float32)
     cu, nc = wine_ctx.cuts(1)
